@@ -70,6 +70,100 @@ int maavss_dft_fwd(const maavss_dft_plan* plan, const float* audio, float* out_c
 int maavss_dft_half_inv(const maavss_dft_plan* plan, const float* in_complex, float* audio, int batch,
                         int norm_forward, void* stream);
 
+
+/* ------------------------------------------------ fusion models: layers, loss, optimiser ------ */
+/* All tensors fp32, contiguous, channels-first (N, C, D, H, W) with D = 1 for the 2-D layers.        */
+
+/* One convolution geometry; shared by Conv2d / Conv3d forward (conv_fwd), their input gradient and the
+ * ConvTranspose2d forward (conv_dgrad), and the weight gradient (conv_wgrad).
+ * nn.Conv2d / nn.BatchNorm2d / nn.Tanh stacks: avse_model.py:427-446,474-502; avse_model_final.py:33-59,75-107;
+ * nn.ConvTranspose2d stacks: avse_model.py:449-464,564-592; avse_model_conv.py:448-464,563-594. */
+typedef struct maavss_conv_desc {
+    int N, Cin, D, H, W;          /* input  (N, Cin, D, H, W) */
+    int Cout, KD, KH, KW;         /* weight (Cout, Cin, KD, KH, KW) */
+    int SD, SH, SW, PD, PH, PW;   /* stride, zero padding */
+    int OD, OH, OW;               /* output (N, Cout, OD, OH, OW); given explicitly so output_padding is expressible */
+} maavss_conv_desc;
+
+/* y = conv(x, w) + bias (bias may be NULL). */
+int maavss_conv_fwd(const maavss_conv_desc* d, const float* x, const float* w, const float* bias, float* y, void* stream);
+/* dx = conv_transpose(dy, w) (+ bias per Cin channel when used as the ConvTranspose forward; may be NULL). */
+int maavss_conv_dgrad(const maavss_conv_desc* d, const float* dy, const float* w, const float* bias, float* dx, void* stream);
+/* dw (+)= sum over batch/positions of dy (x) x.   accumulate != 0 adds into dw (gradient accumulation over num_seq,
+ * train.py:158), else dw is overwritten. */
+int maavss_conv_wgrad(const maavss_conv_desc* d, const float* x, const float* dy, float* dw, int accumulate, void* stream);
+/* out[c] (+)= sum_{n,i} x[n, c, i]   (bias gradients). workspace: maavss_reduce_workspace_bytes(C). */
+int maavss_channel_sum(const float* x, int N, int C, long long inner, float* out, int accumulate, void* workspace, void* stream);
+int maavss_reduce_workspace_bytes(int C);
+
+/* Activations: 0 = identity, 1 = tanh, 2 = leaky_relu(slope), 3 = sigmoid. */
+#define MAAVSS_ACT_NONE 0
+#define MAAVSS_ACT_TANH 1
+#define MAAVSS_ACT_LEAKY 2
+#define MAAVSS_ACT_SIGMOID 3
+
+/* Train-mode BatchNorm (nn.BatchNorm2d / BatchNorm3d, eps 1e-5, momentum 0.1) split so that a data-parallel
+ * caller can all-reduce `partial` between the two halves:
+ *   bn_reduce   : partial[c][s] = {sum x, sum x^2} (double) over split s of the (n, inner) domain; S = maavss_bn_splits().
+ *   bn_finalize : mean / invstd -> stats[c] = {mean, invstd}; running stats and num_batches_tracked updated when
+ *                 running_mean != NULL (count = elements per channel over the WHOLE batch, all ranks).
+ *                 use_running != 0: eval mode, stats come from running_mean / running_var, partial is ignored.
+ *   bn_apply_act: y = act(((x - mean) * invstd) * gamma + beta). */
+int maavss_bn_splits(int N, int C, long long inner);
+int maavss_bn_reduce(const float* x, int N, int C, long long inner, double* partial, void* stream);
+int maavss_bn_finalize(const double* partial, int S, int C, double count, float eps, float momentum, float* running_mean,
+                       float* running_var, long long* num_batches_tracked, int use_running, float* stats, void* stream);
+int maavss_bn_apply_act(const float* x, const float* stats, const float* gamma, const float* beta, int N, int C,
+                        long long inner, int act, float slope, float* y, void* stream);
+/* Backward of act(bn(x)):  dz = dy * act'(y);
+ *   bn_bwd_reduce  : partial[c][s] = {sum dz, sum dz * xhat}
+ *   bn_bwd_finalize: coef[c] = {sum dz / count, sum dz*xhat / count} (zeros in eval mode); dgamma (+)= , dbeta (+)=
+ *   bn_bwd_apply   : dx = gamma * invstd * (dz - coef0 - xhat * coef1). */
+int maavss_bn_bwd_reduce(const float* dy, const float* y, const float* x, const float* stats, int N, int C, long long inner,
+                         int act, float slope, double* partial, void* stream);
+int maavss_bn_bwd_finalize(const double* partial, int S, int C, double count, int eval_mode, float* coef, float* dgamma,
+                           float* dbeta, int accumulate, void* stream);
+int maavss_bn_bwd_apply(const float* dy, const float* y, const float* x, const float* stats, const float* gamma,
+                        const float* coef, int N, int C, long long inner, int act, float slope, float* dx, void* stream);
+
+/* Elementwise activation and its backward (dz = dy * act'(y), from the OUTPUT y). */
+int maavss_act_fwd(const float* x, float* y, long long n, int act, float slope, void* stream);
+int maavss_act_bwd(const float* dy, const float* y, float* dz, long long n, int act, float slope, void* stream);
+
+/* nn.Linear (+ fused activation): y[M, N] = act(x[M, K] w[N, K]^T + bias)   (avse_model.py:550,553,618-627). */
+int maavss_linear_fwd(const float* x, const float* w, const float* bias, float* y, int M, int N, int K, int act, float slope,
+                      void* stream);
+/* dx[M, K] = dz[M, N] w[N, K]   (dx overwritten). */
+int maavss_linear_dgrad(const float* dz, const float* w, float* dx, int M, int N, int K, void* stream);
+/* dw[N, K] (+)= dz[M, N]^T x[M, K];  dbias[N] (+)= sum_m dz (dbias may be NULL). */
+int maavss_linear_wgrad(const float* dz, const float* x, float* dw, float* dbias, int M, int N, int K, int accumulate,
+                        void* stream);
+
+/* nn.LSTM(bias=False, batch_first=True, bidirectional=True, num_layers=1)   (avse_model.py:542-543).
+ * Gate order i, f, g, o.  gin: (2, B, T, 4H) = x w_ih^T per direction (a linear_fwd each).  One launch per time step
+ * handles both directions:  step s uses t = s (dir 0) / T-1-s (dir 1).
+ *   gates: (2, B, T, 4H) post-activation gates (saved for backward)      cells: (2, B, T, H)
+ *   y: (B, T, 2H)   w_hh: two pointers (H4 x H) */
+int maavss_lstm_step_fwd(const float* gin, const float* w_hh_fwd, const float* w_hh_rev, float* gates, float* cells, float* y,
+                         int B, int T, int H, int step, void* stream);
+/* Backward step s (run s = T-1 .. 0): dgates (2, B, T, 4H) receives the pre-activation gate gradients of time t(s);
+ * dcell: (2, B, H) running cell gradient (zero-initialised by the caller). */
+int maavss_lstm_step_bwd(const float* dy, const float* gates, const float* cells, const float* w_hh_fwd, const float* w_hh_rev,
+                         float* dgates, float* dcell, int B, int T, int H, int step, void* stream);
+
+/* nn.MSELoss (mean): loss[0] = mean((a - b)^2)   (train.py:154-156).  workspace: maavss_reduce_workspace_bytes(8). */
+int maavss_mse_fwd(const float* a, const float* b, long long n, float* loss, void* workspace, void* stream);
+/* da (+)= gout[0] * 2 (a - b) / n   (gout is a device scalar: no host sync). */
+int maavss_mse_bwd(const float* a, const float* b, const float* gout, long long n, float* da, int accumulate, void* stream);
+
+/* torch.optim.Adam step (train.py:95,161) over one flat fp32 arena: 28 B/param of HBM traffic.
+ * step_count is the 1-based step number (bias corrections computed on the host in double). grad_scale multiplies g
+ * (1/world_size after a sum all-reduce). */
+int maavss_adam_step(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2, float eps,
+                     float weight_decay, long long step_count, float grad_scale, void* stream);
+/* x[0..n) = value */
+int maavss_fill(float* x, long long n, float value, void* stream);
+
 /* ------------------------------------------------------- motion-attention front end ---------- */
 
 /* av_dataset.py:323-328: per clip, out = attn_diff ? cat(0, diff(attn, dim=0)) : attn, then *= 1/max(out)

@@ -15,6 +15,12 @@ __device__ __forceinline__ float2 cmul(float2 a, float2 b) {
 }
 __device__ __forceinline__ float2 cmul_negi(float2 a) { return make_float2(a.y, -a.x); }  // a * (-i)
 
+// Shared-memory exchange buffers are indexed through pad_idx: one float2 of padding after every 16
+// keeps the stride-16 scatter of the first radix-16 pass (and the stride-NS scatters after it) off a
+// single bank pair.  A buffer for M points needs fft_buf_len(M) float2.
+__device__ __forceinline__ int pad_idx(int x) { return x + (x >> 4); }
+constexpr int fft_buf_len(int M) { return M + M / 16; }
+
 template <int R>
 struct Dft;
 
@@ -135,18 +141,18 @@ __device__ __forceinline__ void fft_pass(const float2 (&v)[16], int i, const flo
         Dft<R>::run(u);
         const int j0 = (j / NS) * (NS * R) + k;
 #pragma unroll
-        for (int q = 0; q < R; ++q) out[j0 + q * NS] = u[q];
+        for (int q = 0; q < R; ++q) out[pad_idx(j0 + q * NS)] = u[q];
     }
 }
 
 template <int M>
 __device__ __forceinline__ void fft_reload(float2 (&v)[16], int i, const float2* __restrict__ buf) {
 #pragma unroll
-    for (int m = 0; m < 16; ++m) v[m] = buf[i + m * (M / 16)];
+    for (int m = 0; m < 16; ++m) v[m] = buf[pad_idx(i + m * (M / 16))];
 }
 
 // Full M-point forward FFT of the 16 values per thread in v (elements i + m*M/16); the natural-
-// order result is left in buf[0..M).  All threads of the block must call (contains barriers).
+// order result is left in buf[pad_idx(0..M)).  All threads of the block must call (contains barriers).
 template <int M>
 __device__ __forceinline__ void fft_forward_block(float2 (&v)[16], int i, const float2* __restrict__ tw,
                                                   float2* __restrict__ buf) {

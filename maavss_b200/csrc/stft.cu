@@ -41,7 +41,7 @@ __global__ void __launch_bounds__(kThreads) stft_fwd_kernel(StftArgs a) {
     float2* bufs = smem + M;
     for (int q = threadIdx.x; q < M; q += kThreads) tw[q] = a.tw[q];
     const int fi = threadIdx.x / TPF, i = threadIdx.x % TPF;
-    float2* buf = bufs + fi * M;
+    float2* buf = bufs + fi * fft_buf_len(M);
     const float* clip = a.audio + (size_t)blockIdx.y * a.n_samples;
     float* out = a.planes + (size_t)blockIdx.y * 2 * a.T_out * a.F_out;
     __syncthreads();
@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(kThreads) istft_kernel(IstftArgs a) {
     extern __shared__ float2 smem[];
     float2* tw = smem;
     float2* bufs = smem + M;
-    float* acc = reinterpret_cast<float*>(bufs + P * M);
+    float* acc = reinterpret_cast<float*>(bufs + P * fft_buf_len(M));
     const int tid = threadIdx.x;
     const int fi = tid / TPF, i = tid % TPF;
     const int hop = a.hop;
@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(kThreads) istft_kernel(IstftArgs a) {
 #pragma unroll
             for (int m = 0; m < 16; ++m) v[m] = make_float2(0.f, 0.f);
         }
-        fft_forward_block<M>(v, i, tw, bufs + fi * M);
+        fft_forward_block<M>(v, i, tw, bufs + fi * fft_buf_len(M));
         const int lo = max(u0, tb * hop);
         const int hi = min(u0 + S_out, t_last * hop + N);
         for (int u = lo + tid; u < hi; u += kThreads) {
@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(kThreads) istft_kernel(IstftArgs a) {
             float s = 0.f;
             for (int tt = tf; tt <= tl; ++tt) {
                 const int j = u - tt * hop;
-                s += istft_frame_sample(bufs + (tt - tb) * M, j) * __ldg(a.window + j);
+                s += istft_frame_sample(bufs + (tt - tb) * fft_buf_len(M), j) * __ldg(a.window + j);
             }
             acc[u - u0] += s;
         }
@@ -162,7 +162,7 @@ __global__ void scale_by_inv_kernel(float* __restrict__ x, long long per_clip, c
 
 __global__ void axpy_kernel(const float* __restrict__ y, const float* __restrict__ noise, float s, float* __restrict__ x, long long n) {
     for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < n; q += (long long)gridDim.x * blockDim.x)
-        x[q] = y[q] + noise[q] * s;
+        x[q] = __fadd_rn(y[q], __fmul_rn(noise[q], s));   // unfused, bit-exact with tensor + noise * std
 }
 
 template <int M>
@@ -172,7 +172,7 @@ int launch_stft(const maavss_stft_plan* p, const StftArgs& a0, int batch, cudaSt
     const int batches = ceil_div(a.T_out, P);
     a.batches_per_cta = ((long long)batches * batch >= 148LL * 32) ? 4 : 1;
     dim3 grid(ceil_div(batches, a.batches_per_cta), batch);
-    const size_t smem = sizeof(float2) * (M + (size_t)P * M);
+    const size_t smem = sizeof(float2) * (M + (size_t)P * fft_buf_len(M));
     MAAVSS_CUDA(cudaFuncSetAttribute(stft_fwd_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     stft_fwd_kernel<M><<<grid, kThreads, smem, st>>>(a);
     MAAVSS_LAUNCH_CHECK();
@@ -188,7 +188,7 @@ int launch_istft(const IstftArgs& a0, int batch, cudaStream_t st) {
     if (G > 64) G = 64;
     a.G = G;
     dim3 grid(ceil_div(a.out_len, (long long)G * a.hop), batch);
-    const size_t smem = sizeof(float2) * (M + (size_t)P * M) + sizeof(float) * (size_t)G * a.hop;
+    const size_t smem = sizeof(float2) * (M + (size_t)P * fft_buf_len(M)) + sizeof(float) * (size_t)G * a.hop;
     MAAVSS_CUDA(cudaFuncSetAttribute(istft_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     istft_kernel<M><<<grid, kThreads, smem, st>>>(a);
     MAAVSS_LAUNCH_CHECK();
@@ -259,8 +259,8 @@ extern "C" int maavss_stft_out_dims(int n_samples, int n_fft, int hop, int trim_
 
 extern "C" int maavss_stft_fwd(const maavss_stft_plan* p, const float* audio, float* planes, int batch,
                                int n_samples, int trim_stft_end, int normalized, int polar, void* stream) {
+    if (batch == 0) return MAAVSS_OK;   // empty batch: torch hands out null data pointers
     MAAVSS_CHECK_ARG(p && audio && planes, "stft_fwd: null argument");
-    if (batch == 0) return MAAVSS_OK;
     MAAVSS_CHECK_ARG(batch > 0 && batch <= 65535, "stft_fwd: batch=%d out of range [0, 65535]", batch);
     StftArgs a;
     int rc = maavss_stft_out_dims(n_samples, p->n_fft, p->hop, trim_stft_end, &a.T_out, &a.F_out);
@@ -282,8 +282,8 @@ extern "C" int maavss_stft_fwd(const maavss_stft_plan* p, const float* audio, fl
 
 extern "C" int maavss_istft_fwd(const maavss_stft_plan* p, const float* planes, float* audio, int batch,
                                 int n_frames, int trim_stft_end, int normalized, int polar, void* stream) {
-    MAAVSS_CHECK_ARG(p && planes && audio, "istft_fwd: null argument");
     if (batch == 0 || n_frames <= 1) return MAAVSS_OK;
+    MAAVSS_CHECK_ARG(p && planes && audio, "istft_fwd: null argument");
     MAAVSS_CHECK_ARG(batch > 0 && batch <= 65535, "istft_fwd: batch=%d out of range [0, 65535]", batch);
     IstftArgs a;
     a.planes = planes;

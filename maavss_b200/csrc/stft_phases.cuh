@@ -56,8 +56,8 @@ __device__ __forceinline__ void stft_post_frame(int i, const float2* __restrict_
             if (i != 0) break;
             k = M / 2;
         }
-        const float2 A = buf[k];
-        const float2 B = buf[(M - k) & (M - 1)];
+        const float2 A = buf[pad_idx(k)];
+        const float2 B = buf[pad_idx((M - k) & (M - 1))];
         const float2 S = make_float2(A.x + B.x, A.y - B.y);   // A + conj(B)
         const float2 D = make_float2(A.x - B.x, A.y + B.y);   // A - conj(B)
         const float2 WD = cmul(tw[k], D);
@@ -118,6 +118,6 @@ __device__ __forceinline__ void istft_load_frame(float2 (&v)[16], int i, const f
 // Sample s (0 <= s < 2M) of the real frame whose FFT(conj Z) sits in buf (natural order), before
 // the 1/M factor:  x[2j] = Re, x[2j+1] = -Im.
 __device__ __forceinline__ float istft_frame_sample(const float2* __restrict__ buf, int s) {
-    const float2 z = buf[s >> 1];
+    const float2 z = buf[pad_idx(s >> 1)];
     return (s & 1) ? -z.y : z.x;
 }

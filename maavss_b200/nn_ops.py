@@ -1,0 +1,395 @@
+"""torch.autograd.Function wrappers over the model-layer entry points of the C ABI (include/maavss_b200.h).
+
+Every forward / backward here is one or a few kernel launches from libmaavss_b200.so on the current CUDA stream;
+there is no PyTorch fallback (CPU tensors raise in _lib.dptr).  Parameter gradients are accumulated IN PLACE into an
+existing ``param.grad`` (the flat gradient arena of optim.FlatParams) -- the gradient-accumulation add of
+train.py:158 is fused into the weight-gradient kernels -- and a fresh tensor is returned only when there is none.
+"""
+import ctypes
+
+import torch
+
+from ._lib import check, dptr, fptr, lib, stream_ptr
+
+ACT_NONE, ACT_TANH, ACT_LEAKY, ACT_SIGMOID = 0, 1, 2, 3
+
+# data-parallel context: set by parallel.init(); when not None, train-mode BatchNorm statistics are all-reduced
+# over this process group so that N ranks reproduce the single-process global-batch result.
+SYNC_BN_GROUP = None
+
+
+class ConvDesc(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int) for n in "N Cin D H W Cout KD KH KW SD SH SW PD PH PW OD OH OW".split()]
+
+
+def _triple(v, fill):
+    v = tuple(v) if isinstance(v, (tuple, list)) else (v, v)
+    return (fill,) + v if len(v) == 2 else v
+
+
+def _null():
+    return ctypes.c_void_p(None)
+
+
+def _opt(t):
+    return fptr(t) if t is not None else _null()
+
+
+def _ws(nbytes, device):
+    return torch.empty((nbytes + 7) // 8, dtype=torch.float64, device=device)
+
+
+def _grad_slot(param, needs):
+    """-> (tensor to write, accumulate flag, value to hand back to autograd)."""
+    if not needs:
+        return None, 0, None
+    g = param.grad
+    if g is not None and g.is_cuda and g.is_contiguous() and g.dtype == torch.float32:
+        return g, 1, None
+    new = torch.empty_like(param, memory_format=torch.contiguous_format)
+    return new, 0, new
+
+
+def make_conv_desc(in_shape5, w_shape5, stride, padding, out_shape3):
+    N, Cin, D, H, W = in_shape5
+    Cout, _, KD, KH, KW = w_shape5
+    return ConvDesc(N, Cin, D, H, W, Cout, KD, KH, KW, *stride, *padding, *out_shape3)
+
+
+def _as5(t):
+    return t if t.dim() == 5 else t.unsqueeze(2)
+
+
+def channel_sum(x5, out, accumulate):
+    N, C = x5.shape[0], x5.shape[1]
+    inner = x5[0, 0].numel() if N else 0
+    ws = _ws(lib().maavss_reduce_workspace_bytes(C), x5.device)
+    check(lib().maavss_channel_sum(fptr(x5), N, C, inner, fptr(out), accumulate, dptr(ws), stream_ptr()))
+
+
+class ConvFn(torch.autograd.Function):
+    """nn.Conv2d / nn.Conv3d forward + backward (zero padding, no dilation / groups)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, stride, padding):
+        nd = x.dim()
+        x5, w5 = _as5(x.contiguous()), _as5(weight)
+        s, p = _triple(stride, 1), _triple(padding, 0)
+        out3 = tuple((x5.shape[2 + i] + 2 * p[i] - w5.shape[2 + i]) // s[i] + 1 for i in range(3))
+        desc = make_conv_desc(x5.shape, w5.shape, s, p, out3)
+        y = torch.empty((x5.shape[0], w5.shape[0]) + out3, device=x.device, dtype=torch.float32)
+        check(lib().maavss_conv_fwd(ctypes.byref(desc), fptr(x5), fptr(w5.contiguous()), _opt(bias), fptr(y), stream_ptr()))
+        ctx.desc, ctx.nd = desc, nd
+        ctx.save_for_backward(x5, weight, bias)
+        return y if nd == 5 else y.squeeze(2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x5, weight, bias = ctx.saved_tensors
+        dy5 = _as5(dy.contiguous())
+        desc = ctx.desc
+        dx = gw = gb = None
+        if ctx.needs_input_grad[0]:
+            dx5 = torch.empty_like(x5)
+            check(lib().maavss_conv_dgrad(ctypes.byref(desc), fptr(dy5), fptr(weight), _null(), fptr(dx5), stream_ptr()))
+            dx = dx5 if ctx.nd == 5 else dx5.squeeze(2)
+        tgt, acc, gw = _grad_slot(weight, ctx.needs_input_grad[1])
+        if tgt is not None:
+            check(lib().maavss_conv_wgrad(ctypes.byref(desc), fptr(x5), fptr(dy5), fptr(tgt), acc, stream_ptr()))
+        if bias is not None:
+            tgt, acc, gb = _grad_slot(bias, ctx.needs_input_grad[2])
+            if tgt is not None:
+                channel_sum(dy5, tgt, acc)
+        return dx, gw, gb, None, None
+
+
+class ConvTransposeFn(torch.autograd.Function):
+    """nn.ConvTranspose2d forward = the input-gradient kernel of the mirrored convolution."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, stride, padding, output_padding):
+        nd = x.dim()
+        x5, w5 = _as5(x.contiguous()), _as5(weight)          # weight: (C_in_t, C_out_t, k..) == conv (Cout, Cin, k..)
+        s, p, op = _triple(stride, 1), _triple(padding, 0), _triple(output_padding, 0)
+        out3 = tuple((x5.shape[2 + i] - 1) * s[i] - 2 * p[i] + w5.shape[2 + i] + op[i] for i in range(3))
+        desc = make_conv_desc((x5.shape[0], w5.shape[1]) + out3, w5.shape, s, p, tuple(x5.shape[2:]))
+        y = torch.empty((x5.shape[0], w5.shape[1]) + out3, device=x.device, dtype=torch.float32)
+        check(lib().maavss_conv_dgrad(ctypes.byref(desc), fptr(x5), fptr(w5.contiguous()), _opt(bias), fptr(y), stream_ptr()))
+        ctx.desc, ctx.nd = desc, nd
+        ctx.save_for_backward(x5, weight, bias)
+        return y if nd == 5 else y.squeeze(2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x5, weight, bias = ctx.saved_tensors
+        dy5 = _as5(dy.contiguous())
+        desc = ctx.desc
+        dx = gw = gb = None
+        if ctx.needs_input_grad[0]:
+            dx5 = torch.empty_like(x5)
+            check(lib().maavss_conv_fwd(ctypes.byref(desc), fptr(dy5), fptr(weight), _null(), fptr(dx5), stream_ptr()))
+            dx = dx5 if ctx.nd == 5 else dx5.squeeze(2)
+        tgt, acc, gw = _grad_slot(weight, ctx.needs_input_grad[1])
+        if tgt is not None:
+            check(lib().maavss_conv_wgrad(ctypes.byref(desc), fptr(dy5), fptr(x5), fptr(tgt), acc, stream_ptr()))
+        if bias is not None:
+            tgt, acc, gb = _grad_slot(bias, ctx.needs_input_grad[2])
+            if tgt is not None:
+                channel_sum(dy5, tgt, acc)
+        return dx, gw, gb, None, None, None
+
+
+def _allreduce_partial(partial):
+    import torch.distributed as dist
+    dist.all_reduce(partial, group=SYNC_BN_GROUP)
+    return dist.get_world_size(SYNC_BN_GROUP)
+
+
+class BNActFn(torch.autograd.Function):
+    """act(BatchNorm(x)) with batch statistics in training (running stats in eval), any channels-first rank."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, running_mean, running_var, nbt, training, momentum, eps, act, slope):
+        x = x.contiguous()
+        N, C = x.shape[0], x.shape[1]
+        inner = x[0, 0].numel() if N else 0
+        L = lib()
+        stats = torch.empty(C, 2, device=x.device, dtype=torch.float32)
+        use_batch = training or running_mean is None
+        S, world = 1, 1
+        if use_batch:
+            S = L.maavss_bn_splits(N, C, inner)
+            partial = torch.empty(C, S, 2, device=x.device, dtype=torch.float64)
+            check(L.maavss_bn_reduce(fptr(x), N, C, inner, dptr(partial), stream_ptr()))
+            if SYNC_BN_GROUP is not None and training:
+                world = _allreduce_partial(partial)
+            count = float(N * inner * world)
+            check(L.maavss_bn_finalize(dptr(partial), S, C, count, eps, momentum if momentum is not None else 0.1,
+                                       _opt(running_mean) if training else _null(), _opt(running_var) if training else _null(),
+                                       dptr(nbt) if (nbt is not None and training) else _null(), 0, fptr(stats), stream_ptr()))
+        else:
+            check(L.maavss_bn_finalize(_null(), 0, C, 1.0, eps, 0.0, fptr(running_mean), fptr(running_var), _null(), 1,
+                                       fptr(stats), stream_ptr()))
+        y = torch.empty_like(x)
+        check(L.maavss_bn_apply_act(fptr(x), fptr(stats), _opt(gamma), _opt(beta), N, C, inner, act, slope, fptr(y), stream_ptr()))
+        ctx.cfg = (N, C, inner, act, slope, use_batch, world)
+        ctx.save_for_backward(x, y, stats, gamma, beta)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, y, stats, gamma, beta = ctx.saved_tensors
+        N, C, inner, act, slope, use_batch, world = ctx.cfg
+        dy = dy.contiguous()
+        L = lib()
+        S = L.maavss_bn_splits(N, C, inner)
+        partial = torch.empty(C, S, 2, device=x.device, dtype=torch.float64)
+        check(L.maavss_bn_bwd_reduce(fptr(dy), fptr(y), fptr(x), fptr(stats), N, C, inner, act, slope, dptr(partial), stream_ptr()))
+        gg_t, gg_acc, gg = _grad_slot(gamma, gamma is not None and ctx.needs_input_grad[1])
+        gb_t, gb_acc, gb = _grad_slot(beta, beta is not None and ctx.needs_input_grad[2])
+        if gg_t is not None and gb_t is not None and gg_acc != gb_acc:      # keep one accumulate flag for the fused finalize
+            gb_t, gb_acc, gb = torch.empty_like(beta), 0, None
+            gb = gb_t
+            if gg_acc:
+                gg_t, gg_acc = torch.empty_like(gamma), 0
+                gg = gg_t
+        if world > 1:
+            # local parameter gradients come from the LOCAL sums (they are averaged by the gradient all-reduce);
+            # the input gradient needs the GLOBAL sums.
+            local = partial.clone()
+            _allreduce_partial(partial)
+            coef = torch.empty(C, 2, device=x.device, dtype=torch.float32)
+            check(L.maavss_bn_bwd_finalize(dptr(local), S, C, float(N * inner), 0, fptr(coef), _opt(gg_t), _opt(gb_t),
+                                           gg_acc if gg_t is not None else gb_acc, stream_ptr()))
+            check(L.maavss_bn_bwd_finalize(dptr(partial), S, C, float(N * inner * world), 0, fptr(coef), _null(), _null(), 0,
+                                           stream_ptr()))
+        else:
+            coef = torch.empty(C, 2, device=x.device, dtype=torch.float32)
+            check(L.maavss_bn_bwd_finalize(dptr(partial), S, C, float(N * inner), 0 if use_batch else 1, fptr(coef), _opt(gg_t),
+                                           _opt(gb_t), gg_acc if gg_t is not None else gb_acc, stream_ptr()))
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            check(L.maavss_bn_bwd_apply(fptr(dy), fptr(y), fptr(x), fptr(stats), _opt(gamma), fptr(coef), N, C, inner, act, slope,
+                                        fptr(dx), stream_ptr()))
+        return dx, gg, gb, None, None, None, None, None, None, None, None
+
+
+class ActFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, act, slope):
+        x = x.contiguous()
+        y = torch.empty_like(x)
+        check(lib().maavss_act_fwd(fptr(x), fptr(y), x.numel(), act, slope, stream_ptr()))
+        ctx.cfg = (act, slope)
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        dy = dy.contiguous()
+        dz = torch.empty_like(dy)
+        check(lib().maavss_act_bwd(fptr(dy), fptr(y), fptr(dz), y.numel(), ctx.cfg[0], ctx.cfg[1], stream_ptr()))
+        return dz, None, None
+
+
+class LinearActFn(torch.autograd.Function):
+    """act(x w^T + b) over the last dimension of x."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, act, slope):
+        shp = x.shape
+        x2 = x.contiguous().reshape(-1, shp[-1])
+        M, K = x2.shape
+        N = weight.shape[0]
+        y = torch.empty(M, N, device=x.device, dtype=torch.float32)
+        check(lib().maavss_linear_fwd(fptr(x2), fptr(weight), _opt(bias), fptr(y), M, N, K, act, slope, stream_ptr()))
+        ctx.cfg = (shp, M, N, K, act, slope)
+        ctx.save_for_backward(x2, weight, bias, y)
+        return y.reshape(*shp[:-1], N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight, bias, y = ctx.saved_tensors
+        shp, M, N, K, act, slope = ctx.cfg
+        dz = dy.contiguous().reshape(M, N)
+        L = lib()
+        if act != ACT_NONE:
+            t = torch.empty_like(dz)
+            check(L.maavss_act_bwd(fptr(dz), fptr(y), fptr(t), dz.numel(), act, slope, stream_ptr()))
+            dz = t
+        dx = gw = gb = None
+        if ctx.needs_input_grad[0]:
+            dx2 = torch.empty(M, K, device=dz.device, dtype=torch.float32)
+            check(L.maavss_linear_dgrad(fptr(dz), fptr(weight), fptr(dx2), M, N, K, stream_ptr()))
+            dx = dx2.reshape(shp)
+        w_t, w_acc, gw = _grad_slot(weight, ctx.needs_input_grad[1])
+        b_t, b_acc, gb = _grad_slot(bias, bias is not None and ctx.needs_input_grad[2])
+        if w_t is not None:
+            if b_t is not None and b_acc != w_acc:          # mixed: give the bias its own pass below
+                check(L.maavss_linear_wgrad(fptr(dz), fptr(x2), fptr(w_t), _null(), M, N, K, w_acc, stream_ptr()))
+                channel_sum(dz.t().contiguous().reshape(1, N, M), b_t, b_acc)
+            else:
+                check(L.maavss_linear_wgrad(fptr(dz), fptr(x2), fptr(w_t), _opt(b_t), M, N, K, w_acc, stream_ptr()))
+        elif b_t is not None:
+            channel_sum(dz.t().contiguous().reshape(1, N, M), b_t, b_acc)
+        return dx, gw, gb, None, None
+
+
+class LSTMFn(torch.autograd.Function):
+    """nn.LSTM(bias=False, batch_first=True, bidirectional=True, num_layers=1): x (B, T, I) -> y (B, T, 2H)."""
+
+    @staticmethod
+    def forward(ctx, x, w_ih_f, w_hh_f, w_ih_r, w_hh_r):
+        x = x.contiguous()
+        B, T, I = x.shape
+        H = w_hh_f.shape[1]
+        L = lib()
+        dev = x.device
+        gin = torch.empty(2, B, T, 4 * H, device=dev, dtype=torch.float32)
+        x2 = x.reshape(B * T, I)
+        for d, w in enumerate((w_ih_f, w_ih_r)):
+            check(L.maavss_linear_fwd(fptr(x2), fptr(w), _null(), fptr(gin[d]), B * T, 4 * H, I, ACT_NONE, 0.0, stream_ptr()))
+        gates = torch.empty_like(gin)
+        cells = torch.empty(2, B, T, H, device=dev, dtype=torch.float32)
+        y = torch.empty(B, T, 2 * H, device=dev, dtype=torch.float32)
+        for s in range(T):
+            check(L.maavss_lstm_step_fwd(fptr(gin), fptr(w_hh_f), fptr(w_hh_r), fptr(gates), fptr(cells), fptr(y), B, T, H, s,
+                                         stream_ptr()))
+        ctx.cfg = (B, T, I, H)
+        ctx.save_for_backward(x2, w_ih_f, w_hh_f, w_ih_r, w_hh_r, gates, cells, y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w_ih_f, w_hh_f, w_ih_r, w_hh_r, gates, cells, y = ctx.saved_tensors
+        B, T, I, H = ctx.cfg
+        L = lib()
+        dev = dy.device
+        dy = dy.contiguous()
+        dgates = torch.empty_like(gates)
+        dcell = torch.zeros(2, B, H, device=dev, dtype=torch.float32)
+        for s in range(T - 1, -1, -1):
+            check(L.maavss_lstm_step_bwd(fptr(dy), fptr(gates), fptr(cells), fptr(w_hh_f), fptr(w_hh_r), fptr(dgates), fptr(dcell),
+                                         B, T, H, s, stream_ptr()))
+        # h_{t-1} of each direction (zero at its first step), as (B*T, H)
+        hprev = torch.zeros(2, B, T, H, device=dev, dtype=torch.float32)
+        hprev[0, :, 1:] = y[:, :-1, :H]
+        hprev[1, :, :-1] = y[:, 1:, H:]
+        grads = [None] * 5
+        dx = None
+        for d, (w_ih, w_hh, i_ih, i_hh) in enumerate(((w_ih_f, w_hh_f, 1, 2), (w_ih_r, w_hh_r, 3, 4))):
+            dg = dgates[d].reshape(B * T, 4 * H)
+            t, acc, grads[i_ih] = _grad_slot(w_ih, ctx.needs_input_grad[i_ih])
+            if t is not None:
+                check(L.maavss_linear_wgrad(fptr(dg), fptr(x2), fptr(t), _null(), B * T, 4 * H, I, acc, stream_ptr()))
+            t, acc, grads[i_hh] = _grad_slot(w_hh, ctx.needs_input_grad[i_hh])
+            if t is not None:
+                check(L.maavss_linear_wgrad(fptr(dg), fptr(hprev[d].reshape(B * T, H)), fptr(t), _null(), B * T, 4 * H, H, acc,
+                                            stream_ptr()))
+            if ctx.needs_input_grad[0]:
+                part = torch.empty(B * T, I, device=dev, dtype=torch.float32)
+                check(L.maavss_linear_dgrad(fptr(dg), fptr(w_ih), fptr(part), B * T, 4 * H, I, stream_ptr()))
+                dx = part if dx is None else dx.add_(part)
+        grads[0] = dx.reshape(B, T, I) if dx is not None else None
+        return tuple(grads)
+
+
+class MSEFn(torch.autograd.Function):
+    """nn.MSELoss() (mean reduction)."""
+
+    @staticmethod
+    def forward(ctx, a, b):
+        a, b = a.contiguous(), b.contiguous()
+        if a.shape != b.shape:
+            raise RuntimeError(f"mse_loss: shapes differ {tuple(a.shape)} vs {tuple(b.shape)}")
+        loss = torch.empty((), device=a.device, dtype=torch.float32)
+        ws = _ws(lib().maavss_reduce_workspace_bytes(8), a.device)
+        check(lib().maavss_mse_fwd(fptr(a), fptr(b), a.numel(), fptr(loss), dptr(ws), stream_ptr()))
+        ctx.save_for_backward(a, b)
+        return loss
+
+    @staticmethod
+    def backward(ctx, gout):
+        a, b = ctx.saved_tensors
+        gout = gout.contiguous().to(torch.float32)
+        da = db = None
+        if ctx.needs_input_grad[0] or ctx.needs_input_grad[1]:
+            da = torch.empty_like(a)
+            check(lib().maavss_mse_bwd(fptr(a), fptr(b), fptr(gout), a.numel(), fptr(da), 0, stream_ptr()))
+            if ctx.needs_input_grad[1]:
+                db = -da
+            if not ctx.needs_input_grad[0]:
+                da = None
+        return da, db
+
+
+def mse_loss(a, b):
+    return MSEFn.apply(a, b)
+
+
+def conv(x, weight, bias, stride, padding):
+    return ConvFn.apply(x, weight, bias, stride, padding)
+
+
+def conv_transpose(x, weight, bias, stride, padding, output_padding):
+    return ConvTransposeFn.apply(x, weight, bias, stride, padding, output_padding)
+
+
+def bn_act(x, bn, act=ACT_NONE, slope=0.0):
+    """bn: an nn.BatchNorm{2,3}d-like module (weight, bias, running_mean, running_var, num_batches_tracked, momentum, eps)."""
+    return BNActFn.apply(x, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.num_batches_tracked, bn.training,
+                         bn.momentum, bn.eps, act, slope)
+
+
+def linear_act(x, weight, bias, act=ACT_NONE, slope=0.0):
+    return LinearActFn.apply(x, weight, bias, act, slope)
+
+
+def activation(x, act, slope=0.0):
+    return ActFn.apply(x, act, slope)
+
+
+def lstm(x, w_ih_f, w_hh_f, w_ih_r, w_hh_r):
+    return LSTMFn.apply(x, w_ih_f, w_hh_f, w_ih_r, w_hh_r)

@@ -13,7 +13,7 @@ static void fft_block_emu(std::vector<float2>& buf /*M*/, const std::vector<floa
     constexpr int R1 = (M / 16 >= 16) ? 16 : (M / 16);
     constexpr int R2 = M / (16 * R1);
     float2 v[16];
-    std::vector<float2> nxt(M);
+    std::vector<float2> nxt(fft_buf_len(M));
     for (int i = 0; i < TPF; ++i) {
         for (int m = 0; m < 16; ++m) v[m] = in_v[i * 16 + m];
         fft_pass<M, 16, 1>(v, i, tw.data(), nxt.data());
@@ -48,7 +48,7 @@ static void stft_emu(const float* clip, int n_samples, int hop, const float* win
     constexpr int TPF = M / 16;
     const int T_out = n_samples / hop;
     auto tw = make_tw(M);
-    std::vector<float2> buf(M), vin(TPF * 16);
+    std::vector<float2> buf(fft_buf_len(M)), vin(TPF * 16);
     for (int t = 0; t < T_out; ++t) {
         for (int i = 0; i < TPF; ++i) {
             float2 v[16];
@@ -80,7 +80,7 @@ static void istft_emu(const float* planes, int T, int F_in, int hop, const float
         int t_lo = (u0 - N + 1 > 0) ? (u0 - N + 1 + hop - 1) / hop : 0;
         int t_hi = min(T - 1, (u0 + S_out - 1) / hop);
         std::vector<float> acc(S_out, 0.f);
-        std::vector<std::vector<float2>> bufs(P, std::vector<float2>(M));
+        std::vector<std::vector<float2>> bufs(P, std::vector<float2>(fft_buf_len(M)));
         for (int tb = t_lo; tb <= t_hi; tb += P) {
             const int t_last = min(tb + P - 1, t_hi);
             for (int fi = 0; fi < P && tb + fi <= t_hi; ++fi) {
