@@ -157,10 +157,11 @@ int maavss_mse_fwd(const float* a, const float* b, long long n, float* loss, voi
 int maavss_mse_bwd(const float* a, const float* b, const float* gout, long long n, float* da, int accumulate, void* stream);
 
 /* torch.optim.Adam step (train.py:95,161) over one flat fp32 arena: 28 B/param of HBM traffic.
- * step_count is the 1-based step number (bias corrections computed on the host in double). grad_scale multiplies g
- * (1/world_size after a sum all-reduce). */
+ * state: 16 device bytes {int64 step; float step_size; float inv_sqrt_bias_correction2}, zero-initialised by the caller;
+ * the step counter is advanced ON THE DEVICE (so a captured CUDA graph of the train step stays correct on replay).
+ * grad_scale multiplies g (1/world_size after a sum all-reduce). */
 int maavss_adam_step(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2, float eps,
-                     float weight_decay, long long step_count, float grad_scale, void* stream);
+                     float weight_decay, void* state, float grad_scale, void* stream);
 /* x[0..n) = value */
 int maavss_fill(float* x, long long n, float value, void* stream);
 
@@ -176,6 +177,13 @@ int maavss_attn_diff_normalise(const float* in, float* out, int clips, int frame
  * divide by the per-frame max -> out (frames, grid_h*patch, grid_w*patch). */
 int maavss_attn_headsum_upsample(const float* cls_rows, float* out, int frames, int heads, int cls_stride,
                                  int grid_h, int grid_w, int patch, void* stream);
+
+/* utilities.video_phasegram (utilities.py:206-228; called on every micro-step, train.py:139):
+ * frames (B, T, H, W) with clip stride batch_stride (elements) -> out (B, T, R*R): antialiased bilinear resize to (R, R), fft2, fftshift over all four dims,
+ * angle, flatten, [cumsum / (2 pi R^2) | (p + pi) / 2 pi], [temporal diff with a zero first frame], [/ max |.| over the
+ * whole tensor].  scratch: B*T*R*R floats; max_ws: 4 bytes. */
+int maavss_video_phasegram(const float* frames, float* out, float* scratch, void* max_ws, int B, int T, int H, int W, int R,
+                           long long batch_stride, int diff, int cumulative, int normalize, void* stream);
 
 #ifdef __cplusplus
 }

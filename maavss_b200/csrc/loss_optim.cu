@@ -46,10 +46,27 @@ __global__ void __launch_bounds__(256) mse_bwd_kernel(const float* __restrict__ 
     }
 }
 
+// Step counter and bias corrections live on the device so that a captured CUDA graph of the whole train step
+// advances them on every replay.
+struct AdamState {
+    long long step;
+    float step_size, inv_bc2_sqrt;
+};
+
+__global__ void adam_prepare_kernel(AdamState* st, float lr, float beta1, float beta2) {
+    const long long step = st->step + 1;
+    st->step = step;
+    const double bc1 = 1.0 - pow((double)beta1, (double)step);
+    const double bc2 = 1.0 - pow((double)beta2, (double)step);
+    st->step_size = (float)((double)lr / bc1);
+    st->inv_bc2_sqrt = (float)(1.0 / sqrt(bc2));
+}
+
 // torch.optim.Adam (no amsgrad, coupled weight decay): 4 reads + 3 writes of 4 B per parameter.
 __global__ void __launch_bounds__(256) adam_kernel(float4* __restrict__ p, const float4* __restrict__ g, float4* __restrict__ m,
                                                    float4* __restrict__ v, long long n4, float beta1, float beta2, float eps,
-                                                   float wd, float step_size, float inv_bc2_sqrt, float gscale) {
+                                                   float wd, const AdamState* __restrict__ st, float gscale) {
+    const float step_size = st->step_size, inv_bc2_sqrt = st->inv_bc2_sqrt;
     for (long long q = (long long)blockIdx.x * 256 + threadIdx.x; q < n4; q += (long long)gridDim.x * 256) {
         float4 pp = p[q], gg = g[q], mm = m[q], vv = v[q];
         float* P = &pp.x;
@@ -72,7 +89,8 @@ __global__ void __launch_bounds__(256) adam_kernel(float4* __restrict__ p, const
 }
 
 __global__ void adam_tail_kernel(float* p, const float* g, float* m, float* v, long long start, long long n, float beta1,
-                                 float beta2, float eps, float wd, float step_size, float inv_bc2_sqrt, float gscale) {
+                                 float beta2, float eps, float wd, const AdamState* __restrict__ st, float gscale) {
+    const float step_size = st->step_size, inv_bc2_sqrt = st->inv_bc2_sqrt;
     const long long q = start + threadIdx.x;
     if (q >= n) return;
     float gr = g[q] * gscale;
@@ -117,23 +135,22 @@ extern "C" int maavss_mse_bwd(const float* a, const float* b, const float* gout,
 }
 
 extern "C" int maavss_adam_step(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2,
-                                float eps, float weight_decay, long long step_count, float grad_scale, void* stream) {
+                                float eps, float weight_decay, void* state, float grad_scale, void* stream) {
     if (n == 0) return MAAVSS_OK;
-    MAAVSS_CHECK_ARG(p && g && m && v && step_count >= 1, "adam_step: bad argument");
+    MAAVSS_CHECK_ARG(p && g && m && v && state, "adam_step: bad argument");
     MAAVSS_CHECK_ARG(((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) % 16 == 0, "adam_step: arenas must be 16-byte aligned");
-    const double bc1 = 1.0 - pow((double)beta1, (double)step_count);
-    const double bc2 = 1.0 - pow((double)beta2, (double)step_count);
-    const float step_size = (float)((double)lr / bc1);
-    const float inv_bc2_sqrt = (float)(1.0 / sqrt(bc2));
     cudaStream_t st = (cudaStream_t)stream;
+    AdamState* as = (AdamState*)state;
+    adam_prepare_kernel<<<1, 1, 0, st>>>(as, lr, beta1, beta2);
+    MAAVSS_LAUNCH_CHECK();
     const long long n4 = n / 4;
     if (n4 > 0) {
         adam_kernel<<<stream_grid(n4, 2), 256, 0, st>>>((float4*)p, (const float4*)g, (float4*)m, (float4*)v, n4, beta1, beta2, eps,
-                                                       weight_decay, step_size, inv_bc2_sqrt, grad_scale);
+                                                       weight_decay, as, grad_scale);
         MAAVSS_LAUNCH_CHECK();
     }
     if (n4 * 4 < n) {
-        adam_tail_kernel<<<1, 32, 0, st>>>(p, g, m, v, n4 * 4, n, beta1, beta2, eps, weight_decay, step_size, inv_bc2_sqrt, grad_scale);
+        adam_tail_kernel<<<1, 32, 0, st>>>(p, g, m, v, n4 * 4, n, beta1, beta2, eps, weight_decay, as, grad_scale);
         MAAVSS_LAUNCH_CHECK();
     }
     return MAAVSS_OK;

@@ -1,0 +1,72 @@
+"""Data-parallel training over the GPUs of one NVSwitch box: one process per GPU, the clip batch sharded
+contiguously across ranks.  The reference is single-process; N-rank semantics are pinned to
+"N ranks == one process on the concatenated batch":
+
+  * gradients: ONE all-reduce (sum) per optimizer step over the flat gradient arena (optim.FlatParams.grad; no
+    bucketing copies, NVLink/NVSwitch makes it bandwidth- not latency-bound), averaged by Adam's grad_scale = 1/W;
+  * train-mode BatchNorm: the per-channel partial sums are all-reduced between the two halves of the BN kernels
+    (nn_ops.BNActFn, `sync_bn=True`), so statistics are those of the global batch;
+  * parameters / buffers are broadcast from rank 0 at start.
+
+torch.distributed (NCCL on GPUs, gloo in the CPU tests) is the plumbing; nothing here touches tensor values on the host.
+"""
+import os
+
+import torch
+import torch.distributed as dist
+
+from . import nn_ops
+
+_GROUP = None
+_WORLD = 1
+
+
+def init(backend=None, sync_bn=True):
+    """Initialise from the torchrun environment (RANK / LOCAL_RANK / WORLD_SIZE / MASTER_*).  Returns (rank, world)."""
+    global _GROUP, _WORLD
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    if world > 1 and not dist.is_initialized():
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        if backend == "nccl":
+            torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        dist.init_process_group(backend=backend, rank=rank, world_size=world)
+    _WORLD = world
+    _GROUP = dist.group.WORLD if world > 1 else None
+    nn_ops.SYNC_BN_GROUP = _GROUP if (sync_bn and world > 1) else None
+    return rank, world
+
+
+def world_size():
+    return _WORLD
+
+
+def shard_bounds(n_items, rank, world):
+    """Contiguous shard [lo, hi) of n_items for `rank`; the first n_items % world ranks get one extra item."""
+    base, rem = divmod(n_items, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def broadcast_module(module, src=0):
+    if _GROUP is None:
+        return
+    for t in list(module.parameters()) + list(module.buffers()):
+        dist.broadcast(t.data, src=src, group=_GROUP)
+
+
+def allreduce_gradients(optimizer):
+    """Sum the flat gradient arena over ranks; the 1/W average is folded into the Adam kernel (grad_scale)."""
+    if _GROUP is None:
+        return
+    dist.all_reduce(optimizer.flat.grad, op=dist.ReduceOp.SUM, group=_GROUP)
+    optimizer.grad_scale = 1.0 / _WORLD
+
+
+def allreduce_max_(t):
+    if _GROUP is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=_GROUP)
+    return t

@@ -1,0 +1,106 @@
+"""One optimizer step of the reference training loops, for a batch that is already resident in HBM.
+
+`FusionTrainStep`  = train.py:132-162            (avse_model.AV_Fusion_Model / avse_model_conv.AV_Fusion_Model):
+    for j in range(num_seq): phasegram of 8 attention frames, 64 STFT frames, forward, MSE(a) + loss_coeff * MSE(v),
+    / num_seq, backward (gradients accumulate in the flat arena); then Adam, zero_grad.
+`FramesTrainStep`  = train_avse_frames.py:150-181 (avse_model_final.AV_Fusion_Model_Frames): raw attention frames in,
+    the middle frame's STFT hops and attention frame as targets.
+
+B200 execution model: the whole step (4 forward/backward micro-steps, the data-parallel gradient all-reduce and the
+Adam kernel) is captured ONCE into a CUDA graph over static input buffers and replayed per step -- no tracing compiler,
+no per-op Python on the replay path.  `graph=False` runs the same code eagerly (what an unchanged train.py does).
+"""
+import torch
+
+from . import nn_ops, parallel, phasegram_ops
+
+
+class _TrainStepBase:
+    def __init__(self, model, optimizer, graph=True, warmup=2):
+        self.model, self.opt = model, optimizer
+        self.use_graph, self.warmup = graph, warmup
+        self._graph, self._static_in, self._static_out = None, None, None
+        self.launches_per_step = None
+
+    def micro_steps(self, *inputs):
+        raise NotImplementedError
+
+    def _eager(self, *inputs):
+        out = self.micro_steps(*inputs)
+        parallel.allreduce_gradients(self.opt)
+        self.opt.step()
+        self.opt.zero_grad()
+        return out
+
+    def _capture(self, inputs):
+        self._static_in = [torch.empty_like(t).copy_(t) for t in inputs]
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            # warm-up on a side stream (allocator / lazy module state); it advances the weights like real steps do
+            for _ in range(self.warmup):
+                self._eager(*self._static_in)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self._graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._graph):
+            self._static_out = self._eager(*self._static_in)
+        # the capture itself did not execute: host mirror of the step counter must not count it
+        self.opt.step_count -= 1
+
+    def __call__(self, *inputs):
+        if not self.use_graph:
+            return self._eager(*inputs)
+        if self._graph is None:
+            self._capture(inputs)
+        for s, t in zip(self._static_in, inputs):
+            if s.data_ptr() != t.data_ptr():
+                s.copy_(t, non_blocking=True)
+        self._graph.replay()
+        self.opt.step_count += 1
+        return self._static_out
+
+    def static_inputs(self):
+        """The graph's input buffers: a producer (H2D copy, front-end kernels) may write them directly."""
+        return self._static_in
+
+
+class FusionTrainStep(_TrainStepBase):
+    def __init__(self, model, optimizer, num_seq=4, num_frames=8, hops_per_frame=8, p_size=64, loss_coeff=0.001, **kw):
+        super().__init__(model, optimizer, **kw)
+        self.num_seq, self.num_frames, self.hpf, self.p_size, self.loss_coeff = num_seq, num_frames, hops_per_frame, p_size, loss_coeff
+
+    def micro_steps(self, x_stft, y_stft, attn):
+        """x_stft, y_stft (B, 2, hpf*(num_frames+num_seq), F); attn (B, 1, num_frames+num_seq, H, W)."""
+        loss = a_loss = v_loss = None
+        for j in range(self.num_seq):
+            pgram = phasegram_ops.video_phasegram(attn[:, :, j:j + self.num_frames], resize=(self.p_size, self.p_size))
+            s0 = self.hpf * j
+            s1 = s0 + self.hpf * self.num_frames
+            yh_a, yh_v, _ = self.model(x_stft[:, :, s0:s1, :], pgram)
+            a_loss = nn_ops.mse_loss(yh_a, y_stft[:, :, s0:s1, :])
+            v_loss = nn_ops.mse_loss(yh_v, pgram)
+            loss = (a_loss + self.loss_coeff * v_loss) / self.num_seq
+            loss.backward()
+        return loss.detach(), a_loss.detach(), v_loss.detach()
+
+
+class FramesTrainStep(_TrainStepBase):
+    def __init__(self, model, optimizer, num_seq=4, num_frames=8, hops_per_frame=8, loss_coeff=0.001, **kw):
+        super().__init__(model, optimizer, **kw)
+        self.num_seq, self.num_frames, self.hpf, self.loss_coeff = num_seq, num_frames, hops_per_frame, loss_coeff
+
+    def micro_steps(self, x_stft, y_stft, attn):
+        loss = a_loss = v_loss = None
+        mid = self.num_frames // 2
+        for j in range(self.num_seq):
+            frames = attn[:, :, j:j + self.num_frames]
+            s0 = self.hpf * j
+            s1 = s0 + self.hpf * self.num_frames
+            m0 = s0 + self.hpf * mid                                   # train_avse_frames.py:158-162
+            yh_a, yh_v, _ = self.model(x_stft[:, :, s0:s1, :], frames)
+            a_loss = nn_ops.mse_loss(yh_a, y_stft[:, :, m0:m0 + self.hpf, :])
+            v_loss = nn_ops.mse_loss(yh_v, attn[:, :, j + mid])
+            loss = (a_loss + self.loss_coeff * v_loss) / self.num_seq
+            loss.backward()
+        return loss.detach(), a_loss.detach(), v_loss.detach()

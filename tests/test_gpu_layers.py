@@ -1,0 +1,216 @@
+"""GPU parity of every model-layer kernel (through the C ABI / autograd wrappers) against the plain PyTorch fp32 op
+it replaces, forward and backward, on seeded inputs.  Tolerances: fp32 kernels, relative to the largest |reference|."""
+import pytest
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module", autouse=True)
+def fp32_reference():
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    yield
+
+
+def rel_err(a, b):
+    return float((a - b).abs().max()) / max(float(b.abs().max()), 1e-12)
+
+
+def g(seed):
+    return torch.Generator().manual_seed(seed)
+
+
+def pair(ours, ref, seed=0):
+    """Copy ref's parameters into ours (same names)."""
+    ours.load_state_dict(ref.state_dict())
+    return ours.cuda(), ref.cuda()
+
+
+CONV_CASES = [
+    # cin, cout, k, s, p, in_hw, batch
+    (2, 8, (5, 5), (2, 2), (2, 2), (64, 128), 3),
+    (8, 32, (5, 5), (2, 2), (2, 2), (32, 64), 2),
+    (64, 64, (5, 5), (1, 2), (2, 2), (8, 16), 4),
+    (1, 2, (1, 9), (1, 2), (0, 4), (8, 512), 3),
+    (32, 64, (1, 9), (1, 2), (0, 4), (8, 128), 2),
+    (2, 4, (3, 9), (2, 2), (1, 3), (64, 129), 2),
+    (5, 7, (3, 3), (1, 1), (0, 0), (9, 11), 2),
+]
+
+
+@pytest.mark.parametrize("cin,cout,k,s,p,hw,B", CONV_CASES)
+@pytest.mark.parametrize("bias", [True, False])
+def test_conv2d(cin, cout, k, s, p, hw, B, bias):
+    from maavss_b200 import layers as L
+    torch.manual_seed(1)
+    ref = nn.Conv2d(cin, cout, k, s, p, bias=bias)
+    ours, ref = pair(L.Conv2d(cin, cout, k, s, p, bias=bias), ref)
+    x = torch.randn(B, cin, *hw, generator=g(2)).cuda()
+    xo, xr = x.clone().requires_grad_(), x.clone().requires_grad_()
+    yo, yr = ours(xo), ref(xr)
+    assert yo.shape == yr.shape
+    assert rel_err(yo, yr) < 2e-6
+    dy = torch.randn(yr.shape, generator=g(3)).cuda()
+    yo.backward(dy)
+    yr.backward(dy)
+    assert rel_err(xo.grad, xr.grad) < 3e-6
+    assert rel_err(ours.weight.grad, ref.weight.grad) < 1e-5
+    if bias:
+        assert rel_err(ours.bias.grad, ref.bias.grad) < 1e-5
+    # accumulation into an existing .grad (gradient accumulation over num_seq)
+    yo2 = ours(xo)
+    yo2.backward(dy)
+    assert rel_err(ours.weight.grad, 2 * ref.weight.grad) < 1e-5
+
+
+def test_conv3d():
+    from maavss_b200 import layers as L
+    torch.manual_seed(1)
+    for cin, cout, pad in ((1, 16, (1, 2, 2)), (16, 8, (1, 3, 3))):
+        ref = nn.Conv3d(cin, cout, (3, 5, 5), 1, pad, bias=False)
+        ours, ref = pair(L.Conv3d(cin, cout, (3, 5, 5), 1, pad, bias=False), ref)
+        x = torch.randn(2, cin, 8, 20, 24, generator=g(4)).cuda()
+        xo, xr = x.clone().requires_grad_(), x.clone().requires_grad_()
+        yo, yr = ours(xo), ref(xr)
+        assert yo.shape == yr.shape and rel_err(yo, yr) < 2e-6
+        dy = torch.randn(yr.shape, generator=g(5)).cuda()
+        yo.backward(dy)
+        yr.backward(dy)
+        assert rel_err(xo.grad, xr.grad) < 3e-6
+        assert rel_err(ours.weight.grad, ref.weight.grad) < 1e-5
+
+
+@pytest.mark.parametrize("cin,cout,k,s,p,op,hw", [
+    (64, 16, (5, 5), (2, 2), (2, 2), (1, 1), (8, 4)),
+    (2, 2, (5, 5), (1, 2), (2, 2), (0, 1), (64, 32)),
+    (64, 32, (1, 9), (1, 2), (0, 4), (0, 1), (8, 4)),
+    (4, 2, (3, 10), (2, 2), (1, 4), (1, 1), (32, 64)),
+])
+def test_conv_transpose2d(cin, cout, k, s, p, op, hw):
+    from maavss_b200 import layers as L
+    torch.manual_seed(1)
+    ref = nn.ConvTranspose2d(cin, cout, k, s, p, output_padding=op)
+    ours, ref = pair(L.ConvTranspose2d(cin, cout, k, s, p, output_padding=op), ref)
+    x = torch.randn(3, cin, *hw, generator=g(6)).cuda()
+    xo, xr = x.clone().requires_grad_(), x.clone().requires_grad_()
+    yo, yr = ours(xo), ref(xr)
+    assert yo.shape == yr.shape and rel_err(yo, yr) < 2e-6
+    dy = torch.randn(yr.shape, generator=g(7)).cuda()
+    yo.backward(dy)
+    yr.backward(dy)
+    assert rel_err(xo.grad, xr.grad) < 3e-6
+    assert rel_err(ours.weight.grad, ref.weight.grad) < 1e-5
+    assert rel_err(ours.bias.grad, ref.bias.grad) < 1e-5
+
+
+@pytest.mark.parametrize("shape", [(4, 8, 32, 64), (16, 64, 8, 4), (3, 2, 8, 2048), (2, 16, 8, 12, 12)])
+@pytest.mark.parametrize("act", ["tanh", "none", "leaky"])
+def test_batchnorm_act(shape, act):
+    from maavss_b200 import layers as L
+    C = shape[1]
+    cls_o, cls_r = (L.BatchNorm3d, nn.BatchNorm3d) if len(shape) == 5 else (L.BatchNorm2d, nn.BatchNorm2d)
+    ref = cls_r(C)
+    with torch.no_grad():
+        ref.weight.copy_(1 + 0.1 * torch.randn(C, generator=g(8)))
+        ref.bias.copy_(0.1 * torch.randn(C, generator=g(9)))
+    ours, ref = pair(cls_o(C), ref)
+    a_o = {"tanh": L.Tanh(), "none": nn.Identity(), "leaky": L.LeakyReLU(0.3)}[act]
+    a_r = {"tanh": nn.Tanh(), "none": nn.Identity(), "leaky": nn.LeakyReLU(0.3)}[act]
+    seq_o = L.FusedSequential(ours, a_o)
+    x = (torch.randn(shape, generator=g(10)) * 1.5 + 0.3).cuda()
+    for train in (True, False):
+        seq_o.train(train)
+        ref.train(train)
+        xo, xr = x.clone().requires_grad_(), x.clone().requires_grad_()
+        yo, yr = seq_o(xo), a_r(ref(xr))
+        assert rel_err(yo, yr) < 5e-6
+        dy = torch.randn(shape, generator=g(11)).cuda()
+        yo.backward(dy)
+        yr.backward(dy)
+        assert rel_err(xo.grad, xr.grad) < 2e-5
+        assert rel_err(ours.weight.grad, ref.weight.grad) < 2e-5
+        assert rel_err(ours.bias.grad, ref.bias.grad) < 2e-5
+        ours.weight.grad = None
+        ours.bias.grad = None
+        ref.zero_grad()
+    assert rel_err(ours.running_mean, ref.running_mean) < 1e-6
+    assert rel_err(ours.running_var, ref.running_var) < 1e-6
+    assert int(ours.num_batches_tracked) == int(ref.num_batches_tracked) == 1
+
+
+@pytest.mark.parametrize("M,K,N", [(16, 4096, 2048), (16, 512, 16384), (1, 2048, 512), (128, 512, 1024), (37, 100, 77)])
+@pytest.mark.parametrize("act", ["leaky", "tanh", "sigmoid", "none"])
+def test_linear(M, K, N, act):
+    from maavss_b200 import layers as L
+    from maavss_b200 import nn_ops as ops
+    torch.manual_seed(2)
+    ref = nn.Linear(K, N)
+    ours, ref = pair(L.Linear(K, N), ref)
+    code = {"leaky": (ops.ACT_LEAKY, 0.3), "tanh": (ops.ACT_TANH, 0.0), "sigmoid": (ops.ACT_SIGMOID, 0.0), "none": (ops.ACT_NONE, 0.0)}[act]
+    fr = {"leaky": lambda t: F.leaky_relu(t, 0.3), "tanh": torch.tanh, "sigmoid": torch.sigmoid, "none": lambda t: t}[act]
+    x = torch.randn(M, K, generator=g(12)).cuda()
+    xo, xr = x.clone().requires_grad_(), x.clone().requires_grad_()
+    yo, yr = ours.fused_forward(xo, *code), fr(ref(xr))
+    assert rel_err(yo, yr) < 5e-6
+    dy = torch.randn(M, N, generator=g(13)).cuda()
+    yo.backward(dy)
+    yr.backward(dy)
+    assert rel_err(xo.grad, xr.grad) < 1e-5
+    assert rel_err(ours.weight.grad, ref.weight.grad) < 1e-5
+    assert rel_err(ours.bias.grad, ref.bias.grad) < 1e-5
+
+
+@pytest.mark.parametrize("B,T,I,H", [(16, 8, 512, 256), (2, 16, 256, 256), (3, 5, 40, 64)])
+def test_lstm(B, T, I, H):
+    from maavss_b200 import layers as L
+    torch.manual_seed(3)
+    kw = dict(input_size=I, hidden_size=H, num_layers=1, bias=False, batch_first=True, bidirectional=True)
+    ref = nn.LSTM(**kw)
+    ours = L.LSTM(**kw)
+    ours.load_state_dict(ref.state_dict())
+    ours, ref = ours.cuda(), ref.cuda()
+    x = torch.randn(B, T, I, generator=g(14)).cuda()
+    xo, xr = x.clone().requires_grad_(), x.clone().requires_grad_()
+    yo, yr = ours(xo)[0], ref(xr)[0]
+    assert yo.shape == yr.shape and rel_err(yo, yr) < 1e-5
+    dy = torch.randn(yr.shape, generator=g(15)).cuda()
+    yo.backward(dy)
+    yr.backward(dy)
+    assert rel_err(xo.grad, xr.grad) < 2e-5
+    for n in ("weight_ih_l0", "weight_hh_l0", "weight_ih_l0_reverse", "weight_hh_l0_reverse"):
+        assert rel_err(getattr(ours, n).grad, getattr(ref, n).grad) < 2e-5, n
+
+
+def test_mse_and_adam():
+    from maavss_b200 import nn_ops as ops
+    from maavss_b200 import optim
+    a = torch.randn(16, 2, 64, 128, generator=g(16)).cuda().requires_grad_()
+    b = torch.randn(16, 2, 64, 128, generator=g(17)).cuda()
+    ar = a.detach().clone().requires_grad_()
+    lo, lr_ = ops.mse_loss(a, b), F.mse_loss(ar, b)
+    assert abs(float(lo) - float(lr_)) < 1e-6 * float(lr_)
+    (lo * 0.25).backward()
+    (lr_ * 0.25).backward()
+    assert rel_err(a.grad, ar.grad) < 1e-6
+    # Adam: 5 steps on three odd-sized tensors vs torch.optim.Adam
+    shapes = [(33, 7), (5,), (128, 65)]
+    po = [nn.Parameter(torch.randn(s, generator=g(18 + i)).cuda()) for i, s in enumerate(shapes)]
+    pr = [nn.Parameter(p.detach().clone()) for p in po]
+    oo = optim.Adam(po, lr=1e-3)
+    orr = torch.optim.Adam(pr, lr=1e-3)
+    for step in range(5):
+        for i, (p, q) in enumerate(zip(po, pr)):
+            gr = torch.randn(p.shape, generator=g(100 + 10 * step + i)).cuda()
+            p.grad.add_(gr)
+            q.grad = gr.clone()
+        oo.step()
+        orr.step()
+        oo.zero_grad()
+        orr.zero_grad()
+    for p, q in zip(po, pr):
+        assert rel_err(p.detach(), q.detach()) < 1e-6
+    sd = oo.state_dict()
+    assert set(sd["state"][0].keys()) == {"step", "exp_avg", "exp_avg_sq"}

@@ -1,0 +1,157 @@
+"""GPU parity of the fusion models (drop-in classes of maavss_b200) against the golden vectors produced by the
+REFERENCE classes (tests/golden/make_golden.py) and against the oracle on the same seeded inputs: outputs, losses,
+gradients of every parameter, BatchNorm running statistics, and two full optimizer steps (train.py:136-162)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import synth
+from conftest import GOLDEN
+from oracle import models as om
+
+pytestmark = pytest.mark.gpu
+
+
+def t(a):
+    return torch.from_numpy(np.asarray(a))
+
+
+def grad_digest(model):
+    names, norms, samples, seen = [], [], [], set()
+    for k, p in model.named_parameters():
+        if p.data_ptr() in seen:
+            continue
+        seen.add(p.data_ptr())
+        names.append(k)
+        if p.grad is None:
+            norms.append(-1.0)
+            samples.append(np.zeros(8, np.float32))
+            continue
+        gr = p.grad.detach().flatten().cpu()
+        norms.append(float(gr.double().norm()))
+        samples.append(gr[synth.sample_idx(gr.numel())].numpy().astype(np.float32))
+    return names, np.array(norms), np.stack(samples)
+
+
+def param_digest(model):
+    out, seen = [], set()
+    for k, p in model.named_parameters():
+        if p.data_ptr() in seen:
+            continue
+        seen.add(p.data_ptr())
+        f = p.detach().flatten().cpu()
+        out.append(np.concatenate(([float(f.double().sum())], f[synth.sample_idx(f.numel())].double().numpy())))
+    return np.stack(out)
+
+
+def micro_step_loss(model, x_a, x_v, y_a, y_v, loss_coeff=0.001, num_seq=4):
+    from maavss_b200.nn_ops import mse_loss
+    yh_a, yh_v, _ = model(x_a, x_v)
+    a_loss, v_loss = mse_loss(yh_a, y_a), mse_loss(yh_v, y_v)
+    return (a_loss + loss_coeff * v_loss) / num_seq, a_loss, v_loss
+
+
+def check_model(g, model, x_a, x_v, y_a, y_v, names_file, sub=None, unused_zero=True):
+    x_a, x_v, y_a, y_v = (z.cuda() for z in (x_a, x_v, y_a, y_v))
+    model.eval()
+    with torch.no_grad():
+        a, v, fz = model(x_a, x_v)
+    torch.testing.assert_close(a.cpu(), t(g["eval_a"]), rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close((v if sub is None else v[..., ::sub]).cpu(), t(g["eval_v"]), rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(fz.cpu(), t(g["eval_fused"]), rtol=1e-4, atol=1e-5)
+    model.train()
+    loss, a_loss, v_loss = micro_step_loss(model, x_a, x_v, y_a, y_v)
+    loss.backward()
+    np.testing.assert_allclose([float(loss), float(a_loss), float(v_loss)], g["losses"], rtol=1e-5)
+    names, norms, samples = grad_digest(model)
+    assert names == open(names_file).read().split()
+    # conv biases that feed a BatchNorm have an exactly-zero gradient: both sides hold only rounding noise (~1e-9) there
+    np.testing.assert_allclose(norms, g["grad_norms"], rtol=2e-3, atol=2e-8)
+    np.testing.assert_allclose(samples, g["grad_samples"], rtol=5e-3, atol=1e-7)
+    bn = np.concatenate([x.flatten().cpu().numpy() for k, x in model.state_dict().items()
+                         if k.endswith("running_mean") or k.endswith("running_var")])
+    np.testing.assert_allclose(bn, g["bn_running"], rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("variant", ["fc", "conv"])
+def test_fusion_model_golden(golden, variant):
+    from maavss_b200 import avse_model, avse_model_conv
+    g = golden("fusion_" + variant)
+    x_a, y_a = synth.stft_batch(2, 64, 128, seed=19)
+    x_v = torch.randn(2, 1, 8, 4096, generator=synth.gen(29)) * 0.3
+    ref = om.AVFusionOracle([2, 2, 64, 128], [2, 1, 8, 4096], 8, variant=variant)
+    sd = synth.fill_state_dict(ref.state_dict(), seed=31)
+    cls = avse_model.AV_Fusion_Model if variant == "fc" else avse_model_conv.AV_Fusion_Model
+    m = cls([2, 2, 64, 128], [2, 1, 8, 4096], 8)
+    assert list(m.state_dict().keys()) == list(sd.keys())           # the state_dict layout IS the API
+    m.load_state_dict(sd)
+    assert next(m.parameters()).is_cuda
+    check_model(g, m, x_a, x_v, y_a, x_v, os.path.join(GOLDEN, f"fusion_{variant}_params.txt"))
+
+
+def test_fusion_train_step_golden(golden):
+    """Two optimizer steps of the reference loop (4 accumulation micro-steps each) with the flat-arena Adam."""
+    from maavss_b200 import avse_model, optim
+    g = golden("fusion_fc_step")
+    ref = om.AVFusionOracle([2, 2, 64, 128], [2, 1, 8, 4096], 8)
+    sd = synth.fill_state_dict(ref.state_dict(), seed=31)
+    m = avse_model.AV_Fusion_Model([2, 2, 64, 128], [2, 1, 8, 4096], 8)
+    m.load_state_dict(sd)
+    m.train()
+    opt = optim.Adam(m.parameters(), lr=1e-5)
+    xs, ys = (z.cuda() for z in synth.stft_batch(2, 96, 128, seed=37))
+    pg = (torch.randn(2, 1, 12, 4096, generator=synth.gen(41)) * 0.3).cuda()
+    losses = []
+    for _ in range(2):
+        for j in range(4):
+            loss, _, _ = micro_step_loss(m, xs[:, :, 8 * j:8 * j + 64].contiguous(), pg[:, :, j:j + 8].contiguous(),
+                                         ys[:, :, 8 * j:8 * j + 64].contiguous(), pg[:, :, j:j + 8].contiguous())
+            loss.backward()
+            losses.append(float(loss))
+        opt.step()
+        opt.zero_grad()
+    np.testing.assert_allclose(losses, g["losses"], rtol=1e-5)
+    # Conv biases that feed a BatchNorm have an exactly-zero gradient; what reaches Adam is rounding noise (~1e-9, below
+    # eps = 1e-8), which Adam turns into a noise-dependent move of up to lr per step -- in the reference as well.  Those
+    # rows get an absolute tolerance of 2 steps * lr; every other parameter is held to 1e-5 relative.
+    names = [k for k, _ in m.named_parameters()]
+    names = [k for i, k in enumerate(names) if k not in names[:i]]
+    mods = dict(m.named_modules())
+    noisy = np.array([k.endswith(".bias") and type(mods[k.rsplit(".", 1)[0]]).__name__.startswith("Conv") for k in names])
+    dig, ref_dig = param_digest(m), g["params"]
+    assert dig.shape[0] == len(names) == noisy.shape[0]
+    np.testing.assert_allclose(dig[~noisy], ref_dig[~noisy], rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(dig[noisy][:, 1:], ref_dig[noisy][:, 1:], rtol=0, atol=2.5e-5)
+
+
+def test_sub_forwards_and_toggles():
+    """audio_ae_forward / visual_ae_forward (ConvTranspose decoders) vs the oracle; toggle_* freeze what they say."""
+    from maavss_b200 import avse_model
+    ref = om.AVFusionOracle([2, 2, 64, 128], [2, 1, 8, 4096], 8)
+    sd = synth.fill_state_dict(ref.state_dict(), seed=5)
+    ref.load_state_dict(sd)
+    m = avse_model.AV_Fusion_Model([2, 2, 64, 128], [2, 1, 8, 4096], 8)
+    m.load_state_dict(sd)
+    x_a, _ = synth.stft_batch(2, 64, 128, seed=6)
+    x_v = torch.randn(2, 1, 8, 4096, generator=synth.gen(7)) * 0.3
+    ref.train()
+    m.train()
+    ya, yv = m.audio_ae_forward(x_a.cuda()), m.visual_ae_forward(x_v.cuda())
+    ra, rv = ref.audio_ae_forward(x_a), ref.visual_ae_forward(x_v)
+    torch.testing.assert_close(ya.cpu(), ra, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(yv.cpu(), rv, rtol=1e-4, atol=1e-5)
+    (ya.square().mean() + yv.square().mean()).backward()
+    (ra.square().mean() + rv.square().mean()).backward()
+    for (k, p), (_, q) in zip(m.named_parameters(), ref.named_parameters()):
+        if q.grad is None:
+            assert p.grad is None, k
+        else:
+            scale = max(float(q.grad.abs().max()), 1e-12)
+            assert float((p.grad.cpu() - q.grad).abs().max()) < 2e-4 * scale + 1e-7, k   # 1e-7: zero-gradient conv biases hold noise
+    m.toggle_enc_grads(False)
+    assert not any(p.requires_grad for p in m.stft_encoder.parameters())
+    assert all(p.requires_grad for p in m.fc1.parameters())
+    m.toggle_fusion_grads(False)
+    assert not any(p.requires_grad for p in m.lstm.parameters())
