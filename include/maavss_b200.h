@@ -21,6 +21,8 @@ extern "C" {
 const char* maavss_last_error(void);
 int maavss_abi_version(void);
 int maavss_device_sm_count(void);
+/* Number of kernels this library has launched (or captured into a CUDA graph) in this process so far. */
+long long maavss_launch_count(void);
 
 /* ------------------------------------------------------------------ audio front end ---------- */
 

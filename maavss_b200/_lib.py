@@ -22,7 +22,7 @@ def parse_header(path=HEADER):
     txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
     txt = re.sub(r"^\s*#.*$", "", txt, flags=re.M)
     protos = {}
-    for m in re.finditer(r"(const char\*|int|void)\s+(maavss_\w+)\s*\(([^;{}]*?)\)\s*;", txt, flags=re.S):
+    for m in re.finditer(r"(const char\*|long long|int|void)\s+(maavss_\w+)\s*\(([^;{}]*?)\)\s*;", txt, flags=re.S):
         ret, name, args = m.group(1), m.group(2), m.group(3)
         argtypes = []
         for a in [x.strip() for x in args.replace("\n", " ").split(",")]:
@@ -44,13 +44,15 @@ def parse_header(path=HEADER):
                 argtypes.append(ctypes.c_double)
             else:
                 raise ValueError(f"unhandled C type in header: {a!r} ({name})")
-        restype = {"int": ctypes.c_int, "void": None, "const char*": ctypes.c_char_p}[ret]
+        restype = {"int": ctypes.c_int, "long long": ctypes.c_longlong, "void": None, "const char*": ctypes.c_char_p}[ret]
         protos[name] = (restype, argtypes)
     return protos
 
 
 def lib():
     global _lib, _protos
+    if _profiler is not None:
+        return _profiler
     if _lib is None:
         if not os.path.exists(LIB_PATH):
             raise RuntimeError(
@@ -66,6 +68,50 @@ def lib():
             raise RuntimeError("libmaavss_b200.so ABI version mismatch")
         _lib = L
     return _lib
+
+
+class _Profiler:
+    """Optional per-call device timing (CUDA events on the launching stream) used by bench.py's roofline leg."""
+    SKIP = {"maavss_last_error", "maavss_abi_version", "maavss_device_sm_count", "maavss_launch_count", "maavss_bn_splits",
+            "maavss_reduce_workspace_bytes", "maavss_stft_out_dims", "maavss_stft_plan_create", "maavss_stft_plan_destroy",
+            "maavss_dft_plan_create", "maavss_dft_plan_destroy"}
+
+    def __init__(self, real):
+        self.real, self.records = real, []
+
+    def __getattr__(self, name):
+        fn = getattr(self.real, name)
+        if name in self.SKIP or not name.startswith("maavss_"):
+            return fn
+        import torch
+
+        def timed(*a):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            rc = fn(*a)
+            e1.record()
+            self.records.append((name, a, e0, e1))
+            return rc
+        return timed
+
+
+_profiler = None
+
+
+def start_profile():
+    global _profiler
+    _profiler = _Profiler(lib())
+    return _profiler
+
+
+def stop_profile():
+    """-> [(entry point, args, milliseconds)] of every call since start_profile()."""
+    global _profiler
+    import torch
+    torch.cuda.synchronize()
+    out = [(n, a, e0.elapsed_time(e1)) for n, a, e0, e1 in _profiler.records]
+    _profiler = None
+    return out
 
 
 def check(rc):

@@ -29,7 +29,13 @@ void maavss_set_error(const char* fmt, ...);
         }                                                                              \
     } while (0)
 
-#define MAAVSS_LAUNCH_CHECK() MAAVSS_CUDA(cudaGetLastError())
+// every kernel launch of the library goes through this macro: it also feeds maavss_launch_count()
+void maavss_count_launch();
+#define MAAVSS_LAUNCH_CHECK()          \
+    do {                               \
+        maavss_count_launch();         \
+        MAAVSS_CUDA(cudaGetLastError()); \
+    } while (0)
 
 static inline int maavss_num_sms() {
     static int n = 0;
