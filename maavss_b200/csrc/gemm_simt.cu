@@ -143,10 +143,18 @@ int launch_gemm(GemmArgs a, int splits, cudaStream_t st) {
 
 }  // namespace
 
+int maavss_skinny_fwd(const float*, const float*, const float*, float*, int, int, int, int, float, cudaStream_t);
+int maavss_skinny_dgrad(const float*, const float*, float*, int, int, int, cudaStream_t);
+int maavss_skinny_wgrad(const float*, const float*, float*, float*, int, int, int, int, cudaStream_t);
+
 extern "C" int maavss_linear_fwd(const float* x, const float* w, const float* bias, float* y, int M, int N, int K, int act,
                                  float slope, void* stream) {
     if (M == 0 || N == 0) return MAAVSS_OK;
     MAAVSS_CHECK_ARG(x && w && y && K > 0, "linear_fwd: bad argument");
+    {
+        const int rc = maavss_skinny_fwd(x, w, bias, y, M, N, K, act, slope, (cudaStream_t)stream);
+        if (rc != 0) return rc < 0 ? rc : MAAVSS_OK;
+    }
     GemmArgs a{};
     a.A = x; a.a_si = K; a.a_sl = 1;
     a.B = w; a.b_sj = K; a.b_sl = 1;
@@ -159,6 +167,10 @@ extern "C" int maavss_linear_fwd(const float* x, const float* w, const float* bi
 extern "C" int maavss_linear_dgrad(const float* dz, const float* w, float* dx, int M, int N, int K, void* stream) {
     if (M == 0 || K == 0) return MAAVSS_OK;
     MAAVSS_CHECK_ARG(dz && w && dx && N > 0, "linear_dgrad: bad argument");
+    {
+        const int rc = maavss_skinny_dgrad(dz, w, dx, M, N, K, (cudaStream_t)stream);
+        if (rc != 0) return rc < 0 ? rc : MAAVSS_OK;
+    }
     // dx[m, k] = sum_n dz[m, n] * w[n, k]:  i = m, j = k, l = n
     GemmArgs a{};
     a.A = dz; a.a_si = N; a.a_sl = 1;
@@ -182,6 +194,10 @@ extern "C" int maavss_linear_wgrad(const float* dz, const float* x, float* dw, f
                                    void* stream) {
     if (N == 0 || K == 0) return MAAVSS_OK;
     MAAVSS_CHECK_ARG(dz && x && dw, "linear_wgrad: bad argument");
+    {
+        const int rc = maavss_skinny_wgrad(dz, x, dw, dbias, M, N, K, accumulate, (cudaStream_t)stream);
+        if (rc != 0) return rc < 0 ? rc : MAAVSS_OK;
+    }
     // dw[n, k] = sum_m dz[m, n] * x[m, k]:  i = n, j = k, l = m ; dbias[n] = sum_m dz[m, n] = row sums of A
     GemmArgs a{};
     a.A = dz; a.a_si = 1; a.a_sl = N;
