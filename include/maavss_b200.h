@@ -103,6 +103,7 @@ int maavss_reduce_workspace_bytes(int C);
 #define MAAVSS_ACT_TANH 1
 #define MAAVSS_ACT_LEAKY 2
 #define MAAVSS_ACT_SIGMOID 3
+#define MAAVSS_ACT_GELU 4   /* erf GELU; tensor-core GEMM epilogue only */
 
 /* Train-mode BatchNorm (nn.BatchNorm2d / BatchNorm3d, eps 1e-5, momentum 0.1) split so that a data-parallel
  * caller can all-reduce `partial` between the two halves:
@@ -131,6 +132,13 @@ int maavss_bn_bwd_apply(const float* dy, const float* y, const float* x, const f
 /* Elementwise activation and its backward (dz = dy * act'(y), from the OUTPUT y). */
 int maavss_act_fwd(const float* x, float* y, long long n, int act, float slope, void* stream);
 int maavss_act_bwd(const float* dy, const float* y, float* dz, long long n, int act, float slope, void* stream);
+
+/* nn.MaxPool3d((1, ph, pw)) (stride = kernel, floor mode; avse_model_final.py:36-57) over the (H, W) plane of each of the
+ * `planes` = N*C*D leading slices.  idx: one byte per output element = arg-max inside its window (row-major). */
+int maavss_maxpool_fwd(const float* x, float* y, unsigned char* idx, long long planes, int H, int W, int ph, int pw,
+                       void* stream);
+int maavss_maxpool_bwd(const float* dy, const unsigned char* idx, float* dx, long long planes, int H, int W, int ph, int pw,
+                       void* stream);
 
 /* nn.Linear (+ fused activation): y[M, N] = act(x[M, K] w[N, K]^T + bias)   (avse_model.py:550,553,618-627). */
 int maavss_linear_fwd(const float* x, const float* w, const float* bias, float* y, int M, int N, int K, int act, float slope,
@@ -179,6 +187,32 @@ int maavss_attn_diff_normalise(const float* in, float* out, int clips, int frame
  * divide by the per-frame max -> out (frames, grid_h*patch, grid_w*patch). */
 int maavss_attn_headsum_upsample(const float* cls_rows, float* out, int frames, int heads, int cls_stride,
                                  int grid_h, int grid_w, int patch, void* stream);
+
+/* ---- DINO ViT-S/8 last-layer attention maps (video_attention.py:38-103 over dino/vision_transformer.py) ----
+ * bf16 operands, fp32 accumulation / residual stream.  All GEMM-shaped work runs on tcgen05 tensor cores fed by TMA.
+ *
+ * tc_gemm_bf16: D[M, N] = A[M, K] B[N, K]^T (+ bias[N]) (-> GELU) (+ residual[M, N] fp32); A, B bf16 row-major with row
+ * pitches lda / ldb (elements, multiples of 8); out fp32 or bf16 with pitch ldc.  nn.Linear of Attention.qkv / proj
+ * (dino/vision_transformer.py:75-78), Mlp.fc1 / fc2 (:51-56) and PatchEmbed.proj as a GEMM (:126-130). */
+int maavss_tc_gemm_bf16(const void* A, const void* B, int M, int N, int K, long long lda, long long ldb, const float* bias,
+                        const float* residual, long long ldr, void* out, long long ldc, int out_bf16, int act, void* stream);
+/* Attention.forward core (dino/vision_transformer.py:82-90): qkv (T, N, 3*heads*64) bf16 -> out (T, N, heads*64) bf16,
+ * out = softmax(q k^T * scale) v per (frame, head); head_dim is 64. */
+int maavss_vit_attention(const void* qkv_bf16, void* out_bf16, int T, int N, int heads, float scale, void* stream);
+/* PatchEmbed operand gather: frames (T, C, H, W) fp32 (top-left gh*P x gw*P crop, video_attention.py:43-47) ->
+ * patches (T*gh*gw, C*P*P) bf16 with column order (c, ky, kx) = Conv2d weight order. */
+int maavss_vit_patchify(const float* frames, void* patches_bf16, int T, int C, int H, int W, int gh, int gw, int P, void* stream);
+/* prepare_tokens (dino/vision_transformer.py:196-207): x (T, 1+np, D) = cat(cls, patch_tok (T*np, D)) + pos (1+np, D). */
+int maavss_vit_assemble_tokens(const float* patch_tok, const float* cls, const float* pos, float* x, int T, int np, int D,
+                               void* stream);
+/* nn.LayerNorm(D, eps) over rows of x fp32 -> y bf16 (Block.norm1 / norm2, dino/vision_transformer.py:98,103). */
+int maavss_layernorm_bf16(const float* x, const float* gamma, const float* beta, void* y_bf16, long long rows, int D, float eps,
+                          void* stream);
+int maavss_f32_to_bf16(const float* in, void* out_bf16, long long n, void* stream);
+/* Last block with the CLS query only (get_last_selfattention, dino/vision_transformer.py:216-223; video_attention.py:56):
+ * q (T rows, pitch ldq) fp32, k (T*N rows, pitch ldk) fp32 -> out (T, heads, N) = softmax_j(q_h . k_jh * scale). */
+int maavss_vit_cls_attn_row(const float* q, long long ldq, const float* k, long long ldk, float* out, int T, int heads, int N,
+                            float scale, void* stream);
 
 /* utilities.video_phasegram (utilities.py:206-228; called on every micro-step, train.py:139):
  * frames (B, T, H, W) with clip stride batch_stride (elements) -> out (B, T, R*R): antialiased bilinear resize to (R, R), fft2, fftshift over all four dims,

@@ -32,6 +32,7 @@ def parse_header(path=HEADER):
             stars = a.count("*")
             base = a.replace("const", "").replace("*", " ").split()
             base = " ".join(base[:-1]) if len(base) > 1 else base[0]
+            base = base.replace("unsigned char", "uchar")
             if stars >= 1:
                 argtypes.append(ctypes.POINTER(ctypes.c_int) if (base == "int" and stars == 1) else ctypes.c_void_p)
             elif base == "int":

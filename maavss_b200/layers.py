@@ -54,6 +54,18 @@ class BatchNorm3d(_BNMixin, nn.BatchNorm3d):
     pass
 
 
+class MaxPool3d(nn.MaxPool3d):
+    """Only the reference's use: kernel (1, ph, pw), stride = kernel, no padding / dilation (avse_model_final.py:36-57)."""
+
+    def forward(self, x):
+        _need_cuda(x)
+        k = self.kernel_size
+        if not (isinstance(k, tuple) and len(k) == 3 and k[0] == 1 and self.stride in (k, None) and self.padding in (0, (0, 0, 0))
+                and self.dilation in (1, (1, 1, 1)) and not self.ceil_mode and not self.return_indices):
+            raise NotImplementedError("maavss_b200.MaxPool3d supports kernel (1, ph, pw) with stride = kernel only")
+        return ops.maxpool(x, k[1], k[2])
+
+
 class Tanh(nn.Tanh):
     ACT = (ops.ACT_TANH, 0.0)
 

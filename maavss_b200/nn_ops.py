@@ -234,6 +234,30 @@ class ActFn(torch.autograd.Function):
         return dz, None, None
 
 
+class MaxPoolFn(torch.autograd.Function):
+    """nn.MaxPool3d((1, ph, pw)) / nn.MaxPool2d((ph, pw)) with stride = kernel (floor mode) over the last two dims."""
+
+    @staticmethod
+    def forward(ctx, x, ph, pw):
+        x = x.contiguous()
+        H, W = x.shape[-2], x.shape[-1]
+        planes = x.numel() // (H * W) if H * W else 0
+        y = torch.empty(x.shape[:-2] + (H // ph, W // pw), device=x.device, dtype=torch.float32)
+        idx = torch.empty(y.shape, device=x.device, dtype=torch.uint8)
+        check(lib().maavss_maxpool_fwd(fptr(x), fptr(y), dptr(idx), planes, H, W, ph, pw, stream_ptr()))
+        ctx.cfg = (tuple(x.shape), planes, H, W, ph, pw)
+        ctx.save_for_backward(idx)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        shape, planes, H, W, ph, pw = ctx.cfg
+        dx = torch.empty(shape, device=dy.device, dtype=torch.float32)
+        check(lib().maavss_maxpool_bwd(fptr(dy.contiguous()), dptr(idx), fptr(dx), planes, H, W, ph, pw, stream_ptr()))
+        return dx, None, None
+
+
 class LinearActFn(torch.autograd.Function):
     """act(x w^T + b) over the last dimension of x."""
 
@@ -381,6 +405,10 @@ def bn_act(x, bn, act=ACT_NONE, slope=0.0):
     """bn: an nn.BatchNorm{2,3}d-like module (weight, bias, running_mean, running_var, num_batches_tracked, momentum, eps)."""
     return BNActFn.apply(x, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.num_batches_tracked, bn.training,
                          bn.momentum, bn.eps, act, slope)
+
+
+def maxpool(x, ph, pw):
+    return MaxPoolFn.apply(x, ph, pw)
 
 
 def linear_act(x, weight, bias, act=ACT_NONE, slope=0.0):

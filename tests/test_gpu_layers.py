@@ -220,3 +220,17 @@ def test_mse_and_adam():
         assert rel_err(p.detach(), q.detach()) < 1e-6
     sd = oo.state_dict()
     assert set(sd["state"][0].keys()) == {"step", "exp_avg", "exp_avg_sq"}
+
+
+@pytest.mark.parametrize("shape,pk", [((2, 16, 8, 64, 64), 2), ((2, 4, 3, 32, 32), 3), ((1, 3, 2, 13, 10), 3), ((2, 2, 1, 12, 12), 3)])
+def test_maxpool3d(shape, pk):
+    from maavss_b200 import layers as L
+    x = torch.randn(*shape, generator=g(30)).cuda()
+    x[0, 0, 0, :4, :4] = 1.5                      # ties: the first maximum of the window takes the gradient
+    xo, xr = x.clone().requires_grad_(), x.clone().requires_grad_()
+    yo, yr = L.MaxPool3d((1, pk, pk))(xo), F.max_pool3d(xr, (1, pk, pk))
+    assert torch.equal(yo, yr)
+    dy = torch.randn(yr.shape, generator=g(31)).cuda()
+    yo.backward(dy)
+    yr.backward(dy)
+    assert torch.equal(xo.grad, xr.grad)

@@ -53,7 +53,7 @@ def micro_step_loss(model, x_a, x_v, y_a, y_v, loss_coeff=0.001, num_seq=4):
     return (a_loss + loss_coeff * v_loss) / num_seq, a_loss, v_loss
 
 
-def check_model(g, model, x_a, x_v, y_a, y_v, names_file, sub=None, unused_zero=True):
+def check_model(g, model, x_a, x_v, y_a, y_v, names_file, sub=None, unused_zero=True, sample_rtol=5e-3):
     x_a, x_v, y_a, y_v = (z.cuda() for z in (x_a, x_v, y_a, y_v))
     model.eval()
     with torch.no_grad():
@@ -69,7 +69,11 @@ def check_model(g, model, x_a, x_v, y_a, y_v, names_file, sub=None, unused_zero=
     assert names == open(names_file).read().split()
     # conv biases that feed a BatchNorm have an exactly-zero gradient: both sides hold only rounding noise (~1e-9) there
     np.testing.assert_allclose(norms, g["grad_norms"], rtol=2e-3, atol=2e-8)
-    np.testing.assert_allclose(samples, g["grad_samples"], rtol=5e-3, atol=1e-7)
+    if sample_rtol <= 5e-3:
+        np.testing.assert_allclose(samples, g["grad_samples"], rtol=sample_rtol, atol=1e-7)
+    else:           # relative to the largest sampled entry of each parameter
+        ref_s = np.asarray(g["grad_samples"])
+        assert (np.abs(samples - ref_s).max(axis=1) <= sample_rtol * np.abs(ref_s).max(axis=1) + 1e-7).all()
     bn = np.concatenate([x.flatten().cpu().numpy() for k, x in model.state_dict().items()
                          if k.endswith("running_mean") or k.endswith("running_var")])
     np.testing.assert_allclose(bn, g["bn_running"], rtol=1e-5, atol=1e-6)
@@ -89,6 +93,36 @@ def test_fusion_model_golden(golden, variant):
     m.load_state_dict(sd)
     assert next(m.parameters()).is_cuda
     check_model(g, m, x_a, x_v, y_a, x_v, os.path.join(GOLDEN, f"fusion_{variant}_params.txt"))
+
+
+def test_frames_model_golden(golden):
+    """avse_model_final.AV_Fusion_Model_Frames (Conv3d + BN3d + MaxPool3d + LeakyReLU visual encoder) vs the reference goldens."""
+    from maavss_b200 import avse_model_final
+    g = golden("frames")
+    xf, yf = synth.stft_batch(2, 64, 129, seed=43)
+    fr = synth.attn_clip(2, 8, 256, 256, seed=47)
+    ref = om.AVFusionFramesOracle([2, 2, 64, 129], [2, 1, 8, 256, 256], 8)
+    sd = synth.fill_state_dict(ref.state_dict(), seed=53)
+    m = avse_model_final.AV_Fusion_Model_Frames([2, 2, 64, 129], [2, 1, 8, 256, 256], 8)
+    assert list(m.state_dict().keys()) == list(sd.keys())
+    m.load_state_dict(sd)
+    # The CPU goldens of the three 2x2-pooled Conv3d blocks carry ~5e-3 of backend noise: the same oracle run through
+    # torch on CUDA differs from them by the same amount (benchmarks/debug_frames2.py), so the golden check is held to
+    # 1e-2 on gradient samples and the tight check is made against the oracle executed on this GPU.
+    check_model(g, m, xf, fr, yf[:, :, 32:40], fr[:, :, 4], os.path.join(GOLDEN, "frames_params.txt"), sample_rtol=1e-2)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    ref.load_state_dict(sd)
+    ref = ref.cuda().train()
+    loss, _, _ = om.micro_step_loss(ref, xf.cuda(), fr.cuda(), yf[:, :, 32:40].cuda(), fr[:, :, 4].cuda())
+    loss.backward()
+    for (k, p), (_, q) in zip(m.named_parameters(), ref.named_parameters()):
+        if q.grad is not None:
+            scale = max(float(q.grad.abs().max()), 1e-12)
+            # arg-max flips of the 2x2 pools under 1e-6 forward noise move ~1e-3 of the early-layer gradients between backends
+            assert float((p.grad - q.grad).abs().max()) < (5e-3 if k.startswith("visual_encoder") else 2e-4) * scale, k
+    with pytest.raises(RuntimeError):
+        avse_model_final.AV_Fusion_Model_Frames([2, 2, 64, 129], [2, 1, 8, 256, 256], 8, latent_channels=64)
 
 
 def test_fusion_train_step_golden(golden):
