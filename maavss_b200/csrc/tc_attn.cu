@@ -6,25 +6,27 @@
 //   pass 2:  S_j recomputed, P_j = exp2((S_j - m) * scale*log2e) written as bf16 into a SWIZZLE_128B smem tile,
 //            O += P_j V_j (V consumed MN-major straight from the qkv layout), row sums accumulated in registers
 //   finally: O / l -> bf16 -> global.  No O rescaling (the maxima are final before pass 2), S never touches HBM.
-// Warp 0: TMA producer, warp 1: UMMA issuer + TMEM owner, warps 2-5: softmax / epilogue (one query row per thread).
+// Warp 0: TMA producer, warp 1: UMMA issuer + TMEM owner, warps 2-9: softmax / epilogue (two threads per query row,
+// each owning 64 of the 128 kv columns of a tile).
 #include "common.cuh"
 #include "tc_common.cuh"
 #include "../../include/maavss_b200.h"
 
 namespace tca {
 
-constexpr int BQ = 128, BKV = 128, HD = 64, KSTAGES = 3, VSTAGES = 2, THREADS = 192;
+constexpr int BQ = 128, BKV = 128, HD = 64, KSTAGES = 3, VSTAGES = 2, THREADS = 320;   // 2 + 8 softmax warps
 constexpr int TILE_BYTES = 128 * HD * 2;                 // 16 KB: 128 tokens x 64 dims bf16
 constexpr int P_BYTES = 2 * TILE_BYTES;                  // 128 x 128 bf16 as two K-major halves of 64 kv
 constexpr int OFF_Q = 0, OFF_K = TILE_BYTES, OFF_V = OFF_K + KSTAGES * TILE_BYTES, OFF_P = OFF_V + VSTAGES * TILE_BYTES;
 constexpr int OFF_BAR = OFF_P + P_BYTES;
-constexpr int SMEM_TOTAL = OFF_BAR + 256 + 1024;
+constexpr int OFF_XCH = OFF_BAR + 256;                   // 2 x 128 floats: row max / row sum exchange between column halves
+constexpr int SMEM_TOTAL = OFF_XCH + 1024 + 1024;
 constexpr int TMEM_COLS = 512;                           // S0 [0,128) S1 [128,256) O [256,320)
 
 __global__ void __launch_bounds__(THREADS, 1) attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __restrict__ out,
                                                               int N, int heads, float scale_log2e) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);    // keeps the shared address space
     uint64_t* bars = (uint64_t*)(smem + OFF_BAR);
     uint64_t* q_full = bars;            // 1
     uint64_t* k_full = bars + 1;        // KSTAGES
@@ -48,8 +50,8 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_kernel(const __grid_const
         tc::mbar_init(q_full, 1);
         for (int s = 0; s < KSTAGES; ++s) { tc::mbar_init(&k_full[s], 1); tc::mbar_init(&k_empty[s], 1); }
         for (int s = 0; s < VSTAGES; ++s) { tc::mbar_init(&v_full[s], 1); tc::mbar_init(&v_empty[s], 1); }
-        for (int b = 0; b < 2; ++b) { tc::mbar_init(&s_full[b], 1); tc::mbar_init(&s_empty[b], 4); }
-        tc::mbar_init(p_full, 4);
+        for (int b = 0; b < 2; ++b) { tc::mbar_init(&s_full[b], 1); tc::mbar_init(&s_empty[b], 8); }
+        tc::mbar_init(p_full, 8);
         tc::mbar_init(p_empty, 1);
         tc::mbar_init(o_full, 1);
         tc::fence_barrier_init();
@@ -124,29 +126,41 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_kernel(const __grid_const
             tc::umma_commit(o_full);
         }
     } else {
-        const int qd = warp & 3;                                  // TMEM lane quadrant
+        // 8 softmax warps: TMEM lane quadrant qd = warp % 4 (one query row per lane), column half hf = which 64 of the
+        // 128 kv columns of every S tile (and which 32 of the 64 output dims) this warp owns.
+        const int qd = warp & 3, hf = (warp - 2) >> 2;
         const int row = qd * 32 + lane;                           // query row inside the tile
         const uint32_t lane_off = (uint32_t)(qd * 32) << 16;
+        float* xch = (float*)(smem + OFF_XCH);
         float m = -INFINITY;
         // ---- pass 1: row maxima of the raw scores
         for (int g = 0; g < nkv; ++g) {
             const int b = g & 1;
             tc::mbar_wait(&s_full[b], (g >> 1) & 1);
             tc::tc_fence_after();
-            const int valid = min(BKV, N - g * BKV);
-#pragma unroll 1
-            for (int c = 0; c < BKV / 32; ++c) {
+            const int valid = N - g * BKV;                        // columns >= valid are beyond the last token
+#pragma unroll
+            for (int c2 = 0; c2 < 2; ++c2) {
+                const int c = hf * 2 + c2;
                 uint32_t r[32];
                 tc::tmem_ld_32x32(tmem + lane_off + b * BKV + c * 32, r);
                 tc::tmem_ld_wait();
+                if (valid >= BKV) {
 #pragma unroll
-                for (int i = 0; i < 32; ++i)
-                    if (c * 32 + i < valid) m = fmaxf(m, __uint_as_float(r[i]));
+                    for (int i = 0; i < 32; ++i) m = fmaxf(m, __uint_as_float(r[i]));
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (c * 32 + i < valid) m = fmaxf(m, __uint_as_float(r[i]));
+                }
             }
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&s_empty[b]);
         }
+        xch[hf * 128 + row] = m;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        m = fmaxf(m, xch[(hf ^ 1) * 128 + row]);
         const float mb = m * scale_log2e;
         float l = 0.f;
         // ---- pass 2: P = exp2(S * scale*log2e - m * scale*log2e) -> bf16 -> swizzled smem tile
@@ -155,28 +169,32 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_kernel(const __grid_const
             tc::mbar_wait(&s_full[b], (g >> 1) & 1);
             tc::mbar_wait(p_empty, (j & 1) ^ 1);
             tc::tc_fence_after();
-            const int valid = min(BKV, N - j * BKV);
-#pragma unroll 1
-            for (int c = 0; c < BKV / 32; ++c) {
+            const int valid = N - j * BKV;
+            // this warp's 64 kv columns are the K-major half `hf` of the P tile: one 128-byte row per query
+            uint8_t* prow = smem + OFF_P + hf * TILE_BYTES + row * 128;
+#pragma unroll
+            for (int c2 = 0; c2 < 2; ++c2) {
+                const int c = hf * 2 + c2;
                 uint32_t r[32];
                 tc::tmem_ld_32x32(tmem + lane_off + b * BKV + c * 32, r);
                 tc::tmem_ld_wait();
                 uint32_t packed[16];
 #pragma unroll
                 for (int i = 0; i < 32; i += 2) {
-                    float p0 = (c * 32 + i < valid) ? exp2f(fmaf(__uint_as_float(r[i]), scale_log2e, -mb)) : 0.f;
-                    float p1 = (c * 32 + i + 1 < valid) ? exp2f(fmaf(__uint_as_float(r[i + 1]), scale_log2e, -mb)) : 0.f;
+                    float p0 = exp2f(fmaf(__uint_as_float(r[i]), scale_log2e, -mb));
+                    float p1 = exp2f(fmaf(__uint_as_float(r[i + 1]), scale_log2e, -mb));
+                    if (valid < BKV) {
+                        if (c * 32 + i >= valid) p0 = 0.f;
+                        if (c * 32 + i + 1 >= valid) p1 = 0.f;
+                    }
+                    l += p0 + p1;
                     const __nv_bfloat162 pk = __floats2bfloat162_rn(p0, p1);
-                    // the row sum uses the bf16-rounded values that the PV product will see
-                    l += __bfloat162float(pk.x) + __bfloat162float(pk.y);
                     packed[i >> 1] = *reinterpret_cast<const uint32_t*>(&pk);
                 }
-                // 32 kv = 64 bytes = four 16-byte chunks of this row; half = (c >> 1), chunk index inside the 128-byte row
-                uint8_t* half = smem + OFF_P + (c >> 1) * TILE_BYTES + row * 128;
 #pragma unroll
                 for (int ch = 0; ch < 4; ++ch) {
-                    const int chunk = (c & 1) * 4 + ch;
-                    *reinterpret_cast<uint4*>(half + ((chunk ^ (row & 7)) << 4)) =
+                    const int chunk = c2 * 4 + ch;
+                    *reinterpret_cast<uint4*>(prow + ((chunk ^ (row & 7)) << 4)) =
                         make_uint4(packed[ch * 4], packed[ch * 4 + 1], packed[ch * 4 + 2], packed[ch * 4 + 3]);
                 }
             }
@@ -188,18 +206,21 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_kernel(const __grid_const
                 tc::mbar_arrive(p_full);
             }
         }
-        // ---- epilogue: O / l
+        asm volatile("bar.sync 1, 256;" ::: "memory");        // both halves are done reading the maxima
+        xch[hf * 128 + row] = l;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        l += xch[(hf ^ 1) * 128 + row];
+        // ---- epilogue: O / l, this warp's 32 of the 64 output dims
         tc::mbar_wait(o_full, 0);
         tc::tc_fence_after();
         const float inv = 1.f / l;
         const int qrow = q0 + row;
-#pragma unroll 1
-        for (int c = 0; c < HD / 32; ++c) {
+        {
             uint32_t r[32];
-            tc::tmem_ld_32x32(tmem + lane_off + 2 * BKV + c * 32, r);
+            tc::tmem_ld_32x32(tmem + lane_off + 2 * BKV + hf * 32, r);
             tc::tmem_ld_wait();
             if (qrow < N) {
-                __nv_bfloat16* dst = out + ((size_t)f * N + qrow) * D + h * HD + c * 32;
+                __nv_bfloat16* dst = out + ((size_t)f * N + qrow) * D + h * HD + hf * 32;
 #pragma unroll
                 for (int i = 0; i < 32; i += 8) {
                     uint32_t w[4];

@@ -2,7 +2,7 @@
 // ViT-S/8 attention-map extractor (dino/vision_transformer.py:59-65 Mlp, :80-92 Attention qkv/proj, :116-131 PatchEmbed):
 //     D[M, N] = A[M, K] . B[N, K]^T (+ bias[N]) (-> GELU) (+ residual[M, N])     A, B bf16 K-major, fp32 accumulate in TMEM
 // One CTA per SM loops over 128 x BN output tiles.  Warp 0: TMA producer (SWIZZLE_128B boxes of 64 bf16 along K into a
-// 5-stage mbarrier ring).  Warp 1: allocates TMEM and issues tcgen05.mma (UMMA 128 x BN x 16) into one of two
+// 4/5-stage mbarrier ring).  Warp 1: allocates TMEM and issues tcgen05.mma (UMMA 128 x BN x 16) into one of two
 // accumulator stages.  Warps 2-5: epilogue, each owning its TMEM lane quadrant: tcgen05.ld -> smem transpose ->
 // fused bias / GELU / residual -> coalesced stores, overlapped with the next tile's main loop.
 #include "common.cuh"
@@ -11,13 +11,14 @@
 
 namespace tcg {
 
-constexpr int BM = 128, BK = 64, STAGES = 5, ACC_STAGES = 2, THREADS = 192;
+constexpr int BM = 128, BK = 64, ACC_STAGES = 2, THREADS = 192;
 
 template <int BN>
 struct Smem {
+    static constexpr int STAGES = BN > 128 ? 4 : 5;
     static constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int EPI_BYTES = 4 * 32 * 33 * 4;
+    static constexpr int EPI_BYTES = 4 * 32 * 32 * 4;
     static constexpr int BAR_OFF = STAGES * STAGE_BYTES + EPI_BYTES;
     static constexpr int TOTAL = BAR_OFF + 256 + 1024;    // barriers + tmem slot, + slack for the 1024-byte alignment
 };
@@ -39,8 +40,10 @@ __global__ void __launch_bounds__(THREADS, 1) tc_gemm_kernel(const __grid_consta
                                                              const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
                                                              Epilogue ep) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);    // keeps the shared address space
     using S = Smem<BN>;
+    constexpr int STAGES = S::STAGES;
+    constexpr int TMEM_COLS = ACC_STAGES * BN <= 128 ? 128 : (ACC_STAGES * BN <= 256 ? 256 : 512);
     float* epi = (float*)(smem + STAGES * S::STAGE_BYTES);
     uint64_t* full = (uint64_t*)(smem + S::BAR_OFF);
     uint64_t* empty = full + STAGES;
@@ -66,7 +69,7 @@ __global__ void __launch_bounds__(THREADS, 1) tc_gemm_kernel(const __grid_consta
         }
         tc::fence_barrier_init();
     }
-    if (warp == 1) tc::tmem_alloc(tmem_slot, ACC_STAGES * BN);
+    if (warp == 1) tc::tmem_alloc(tmem_slot, TMEM_COLS);
     tc::tc_fence_before();
     __syncthreads();
     tc::tc_fence_after();
@@ -116,7 +119,8 @@ __global__ void __launch_bounds__(THREADS, 1) tc_gemm_kernel(const __grid_consta
         }
     } else {
         const int q = warp & 3;                      // TMEM lane quadrant this warp may access
-        float* stage = epi + q * (32 * 33);
+        float* stage = epi + q * (32 * 32);          // 32 rows x 32 fp32, 16-byte chunks XOR-swizzled by (row & 7)
+        const int sub = lane >> 3, cc = (lane & 7) * 4;     // phase 2: 4 rows per pass, 8 lanes x float4 per row
         int it = 0;
         for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++it) {
             const int m0 = (t / n_tiles) * BM, n0 = (t % n_tiles) * BN;
@@ -130,20 +134,39 @@ __global__ void __launch_bounds__(THREADS, 1) tc_gemm_kernel(const __grid_consta
                 tc::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + a * BN + c * 32, r);
                 tc::tmem_ld_wait();
 #pragma unroll
-                for (int j = 0; j < 32; ++j) stage[lane * 33 + j] = __uint_as_float(r[j]);
+                for (int j = 0; j < 8; ++j)
+                    *reinterpret_cast<uint4*>(&stage[lane * 32 + ((j ^ (lane & 7)) << 2)]) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
                 __syncwarp();
-                const int col = n0 + c * 32 + lane;
-                if (col < N) {
-                    const float b = ep.bias ? __ldg(ep.bias + col) : 0.f;
-#pragma unroll 4
-                    for (int rr = 0; rr < 32; ++rr) {
+                const int col = n0 + c * 32 + cc;
+                if (col < N) {                       // N % 4 == 0: the float4 is entirely inside or outside
+                    float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (ep.bias) b4 = __ldg(reinterpret_cast<const float4*>(ep.bias + col));
+                    float4 res[8];
+                    if (ep.residual) {               // all residual loads in flight before the first store (out may alias residual)
+#pragma unroll
+                        for (int p = 0; p < 8; ++p) {
+                            const int row = m0 + q * 32 + p * 4 + sub;
+                            res[p] = row < M ? *reinterpret_cast<const float4*>(ep.residual + (size_t)row * ep.ldr + col)
+                                             : make_float4(0.f, 0.f, 0.f, 0.f);
+                        }
+                    }
+#pragma unroll
+                    for (int p = 0; p < 8; ++p) {
+                        const int rr = p * 4 + sub;
                         const int row = m0 + q * 32 + rr;
-                        if (row >= M) break;
-                        float v = stage[rr * 33 + lane] + b;
-                        if (ep.act == MAAVSS_ACT_GELU) v = gelu_erf(v);
-                        if (ep.residual) v += ep.residual[(size_t)row * ep.ldr + col];
-                        if (ep.out_bf16) ((__nv_bfloat16*)ep.out)[(size_t)row * ep.ldc + col] = __float2bfloat16(v);
-                        else ((float*)ep.out)[(size_t)row * ep.ldc + col] = v;
+                        float4 v = *reinterpret_cast<const float4*>(&stage[rr * 32 + (((lane & 7) ^ (rr & 7)) << 2)]);
+                        v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w;
+                        if (ep.act == MAAVSS_ACT_GELU) { v.x = gelu_erf(v.x); v.y = gelu_erf(v.y); v.z = gelu_erf(v.z); v.w = gelu_erf(v.w); }
+                        if (ep.residual) { v.x += res[p].x; v.y += res[p].y; v.z += res[p].z; v.w += res[p].w; }
+                        if (row < M) {
+                            if (ep.out_bf16) {
+                                const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+                                *reinterpret_cast<uint2*>((__nv_bfloat16*)ep.out + (size_t)row * ep.ldc + col) =
+                                    make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi));
+                            } else {
+                                *reinterpret_cast<float4*>((float*)ep.out + (size_t)row * ep.ldc + col) = v;
+                            }
+                        }
                     }
                 }
                 __syncwarp();
@@ -155,7 +178,7 @@ __global__ void __launch_bounds__(THREADS, 1) tc_gemm_kernel(const __grid_consta
     }
     tc::tc_fence_before();
     __syncthreads();
-    if (warp == 1) tc::tmem_dealloc(tmem_base, ACC_STAGES * BN);
+    if (warp == 1) tc::tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
 }  // namespace tcg
@@ -220,6 +243,10 @@ extern "C" int maavss_tc_gemm_bf16(const void* A, const void* B, int M, int N, i
     MAAVSS_CHECK_ARG(A && B && out && K > 0, "tc_gemm_bf16: bad argument");
     MAAVSS_CHECK_ARG(act == MAAVSS_ACT_NONE || act == MAAVSS_ACT_GELU, "tc_gemm_bf16: activation %d not supported", act);
     tcg::Epilogue ep{bias, residual, ldr, out, ldc, out_bf16, act};
+    MAAVSS_CHECK_ARG(N % 4 == 0 && ldc % 4 == 0 && (residual == nullptr || ldr % 4 == 0) && ((uintptr_t)out & 15) == 0 &&
+                         ((uintptr_t)residual & 15) == 0 && ((uintptr_t)bias & 15) == 0,
+                     "tc_gemm_bf16: N and the output / residual pitches must be multiples of 4 and 16-byte aligned");
     if (N <= 64) return launch_tc_gemm<64>(A, B, M, N, K, lda, ldb, ep, (cudaStream_t)stream);
+    if (N % 192 == 0) return launch_tc_gemm<192>(A, B, M, N, K, lda, ldb, ep, (cudaStream_t)stream);
     return launch_tc_gemm<128>(A, B, M, N, K, lda, ldb, ep, (cudaStream_t)stream);
 }
