@@ -129,6 +129,27 @@ int maavss_bn_bwd_finalize(const double* partial, int S, int C, double count, in
 int maavss_bn_bwd_apply(const float* dy, const float* y, const float* x, const float* stats, const float* gamma,
                         const float* coef, int N, int C, long long inner, int act, float slope, float* dx, void* stream);
 
+/* Two-launch train-mode BatchNorm (+ activation) over `groups` independent sub-batches of N/groups samples, each with
+ * its own batch statistics: the num_seq accumulation windows of one optimizer step (train.py:136-159) batched into one
+ * pass (groups = 1 is the plain layer).  reduce -> [data-parallel all-reduce of `partial`] -> apply; the apply kernels
+ * re-derive the statistics from the partials themselves (no finalize launch).
+ *   partial: (groups, C, S, 2) doubles, S = maavss_bn_splits(N/groups, C, inner);  count = elements per (group, channel)
+ *   over ALL ranks;  stats (groups, C, 2) = {mean, invstd} is written by apply and saved for the backward.
+ *   Running statistics receive the `groups` momentum updates in window order; num_batches_tracked += groups. */
+int maavss_bn_reduce_grouped(const float* x, int N, int C, long long inner, int groups, double* partial, void* stream);
+int maavss_bn_apply_grouped(const float* x, const double* partial, int N, int C, long long inner, int groups, double count,
+                            const float* gamma, const float* beta, float* running_mean, float* running_var,
+                            long long* num_batches_tracked, float momentum, float eps, int act, float slope, float* stats, float* y,
+                            void* stream);
+int maavss_bn_bwd_reduce_grouped(const float* dy, const float* y, const float* x, const float* stats, int N, int C, long long inner,
+                                 int groups, int act, float slope, double* partial, void* stream);
+/* partial: sums used for the input gradient (all-reduced when data parallel); partial_local: this rank's sums, used for
+ * dgamma / dbeta (+)= (may be the same pointer).  dx may be NULL. */
+int maavss_bn_bwd_apply_grouped(const float* dy, const float* y, const float* x, const float* stats, const float* gamma,
+                                const double* partial, const double* partial_local, int N, int C, long long inner, int groups,
+                                double count, int act, float slope, float* dgamma, float* dbeta, int accumulate, float* dx,
+                                void* stream);
+
 /* Elementwise activation and its backward (dz = dy * act'(y), from the OUTPUT y). */
 int maavss_act_fwd(const float* x, float* y, long long n, int act, float slope, void* stream);
 int maavss_act_bwd(const float* dy, const float* y, float* dz, long long n, int act, float slope, void* stream);

@@ -19,23 +19,14 @@ struct Geo {
     int k_per_split;
 };
 
-// value of the "position x tap" operand: FWD/WGRAD gather from the conv input, DGRAD gathers from dy.
-template <int MODE>
-__device__ __forceinline__ float gather(const Geo& g, const float* __restrict__ src, int n, int a, int b, int c, int ch, int tap) {
-    const maavss_conv_desc& d = g.d;
-    const int kd = tap / g.KHW, r = tap - kd * g.KHW;
-    const int kh = r / d.KW, kw = r - kh * d.KW;
-    if (MODE == DGRAD) {
-        int td = a + d.PD - kd, th = b + d.PH - kh, tw = c + d.PW - kw;
-        if (td < 0 || th < 0 || tw < 0) return 0.f;
-        const int od = td / d.SD, oh = th / d.SH, ow = tw / d.SW;
-        if (od * d.SD != td || oh * d.SH != th || ow * d.SW != tw || od >= d.OD || oh >= d.OH || ow >= d.OW) return 0.f;
-        return __ldg(src + ((size_t)n * d.Cout + ch) * g.O + (size_t)od * g.OHW + oh * d.OW + ow);
-    } else {
-        const int id = a * d.SD - d.PD + kd, ih = b * d.SH - d.PH + kh, iw = c * d.SW - d.PW + kw;
-        if (id < 0 || id >= d.D || ih < 0 || ih >= d.H || iw < 0 || iw >= d.W) return 0.f;
-        return __ldg(src + ((size_t)n * d.Cin + ch) * g.I + (size_t)id * g.HW + ih * d.W + iw);
-    }
+constexpr int LT = 256;        // K-index decode table window (FWD / DGRAD)
+
+__device__ __forceinline__ bool div_stride(int t, int S, int& q) {   // t / S when exact and t >= 0 (S is warp-uniform)
+    if (t < 0) return false;
+    if (S == 1) { q = t; return true; }
+    if (S == 2) { q = t >> 1; return (t & 1) == 0; }
+    q = t / S;
+    return q * S == t;
 }
 
 template <int MODE, int TM, int TN, int TJ>
@@ -44,8 +35,13 @@ __global__ void __launch_bounds__(256) conv_igemm_kernel(Geo g, const float* __r
     // FWD:   act = x,  wgt_or_dy = w,  out = y          rows i = positions, cols j = cout, l = ci*KV + tap
     // DGRAD: act = dy, wgt_or_dy = w,  out = dx         rows i = input positions, cols j = cin, l = co*KV + tap
     // WGRAD: act = x,  wgt_or_dy = dy, out = dw         rows i = cout, cols j = ci*KV + tap, l = positions
+    // All index decoding (div/mod) is hoisted out of the gather loops into small shared-memory tables:
+    //   FWD/DGRAD: ltab[l] = {channel offset (+ tap offset for FWD), packed (kd, kh, kw)} for a window of LT reduction indices;
+    //   WGRAD:     ptab[l] = {input base offset, packed (id0, ih0, iw0), dy base offset} for the BK positions of an iteration.
     __shared__ float As[BK][TM + 4];
     __shared__ float Bs[BK][TN + 4];
+    __shared__ int4 ltab[MODE == WGRAD ? 1 : LT];
+    __shared__ int4 ptab[MODE == WGRAD ? 2 * BK : 1];
     constexpr int TI = 256 / TJ;                        // thread grid TI x TJ
     constexpr int RM = TM / TI, RN = TN / TJ;          // per-thread micro tile
     static_assert(TM % TI == 0 && TN % TJ == 0 && 256 % TM == 0 && 256 % TN == 0, "bad tile");
@@ -54,37 +50,63 @@ __global__ void __launch_bounds__(256) conv_igemm_kernel(Geo g, const float* __r
     const int ti = threadIdx.x % TI, tj = threadIdx.x / TI;
     const int l_begin = blockIdx.z * g.k_per_split;
     const int l_end = min(g.Kdim, l_begin + g.k_per_split);
-
-    // ---- per-thread fixed decode of the gathered operand's position (one position per thread)
-    // FWD / DGRAD: gathered operand is A (row = position).  WGRAD: gathered operand is B, position = l (varies) and the
-    // fixed per-thread quantity is the column j = (ci, tap).
     constexpr int A_PER = (TM * BK + 255) / 256, B_PER = (TN * BK + 255) / 256;
-    int pn = 0, pa = 0, pb = 0, pc = 0;
+
+    // ---- per-thread fixed part of the gathered operand
+    int p_base = 0, p_a = 0, p_b = 0, p_c = 0;          // FWD: input base offset and (id0, ih0, iw0); DGRAD: n*Cout*O and (td0, th0, tw0)
     bool pvalid = false;
     if (MODE != WGRAD) {
-        const int r = threadIdx.x % TM;
-        const int p = i0 + r;
+        const int p = i0 + (int)(threadIdx.x % TM);
         pvalid = p < g.Mdim;
         const int ext = (MODE == FWD) ? g.O : g.I;
         const int plane = (MODE == FWD) ? g.OHW : g.HW;
         const int wdt = (MODE == FWD) ? d.OW : d.W;
         const int pp = pvalid ? p : 0;
-        pn = pp / ext;
-        int o = pp - pn * ext;
-        pa = o / plane;
-        o -= pa * plane;
-        pb = o / wdt;
-        pc = o - pb * wdt;
+        const int n = pp / ext;
+        int o = pp - n * ext;
+        const int a = o / plane;
+        o -= a * plane;
+        const int b = o / wdt, c = o - b * wdt;
+        if (MODE == FWD) {
+            p_a = a * d.SD - d.PD; p_b = b * d.SH - d.PH; p_c = c * d.SW - d.PW;
+            p_base = n * d.Cin * g.I + p_a * g.HW + p_b * d.W + p_c;
+        } else {
+            p_a = a + d.PD; p_b = b + d.PH; p_c = c + d.PW;
+            p_base = n * d.Cout * g.O;
+        }
     }
-    int wci = 0, wtap = 0;
+    int w_off = 0, w_kd = 0, w_kh = 0, w_kw = 0;        // WGRAD: this thread's column (ci, tap)
     bool wvalid = false;
     if (MODE == WGRAD) {
-        const int c = threadIdx.x % TN;
-        const int j = j0 + c;
+        const int j = j0 + (int)(threadIdx.x % TN);
         wvalid = j < g.Ndim;
-        wci = (wvalid ? j : 0) / g.KV;
-        wtap = (wvalid ? j : 0) - wci * g.KV;
+        const int jj = wvalid ? j : 0;
+        const int ci = jj / g.KV, tap = jj - ci * g.KV;
+        w_kd = tap / g.KHW;
+        const int r = tap - w_kd * g.KHW;
+        w_kh = r / d.KW;
+        w_kw = r - w_kh * d.KW;
+        w_off = ci * g.I + w_kd * g.HW + w_kh * d.W + w_kw;
     }
+    auto fill_ptab = [&](int l0, int buf) {             // WGRAD: decode the BK positions of the iteration starting at l0
+        if (threadIdx.x < BK) {
+            const int p = l0 + threadIdx.x;
+            int4 e = make_int4(0, 0, -1, 0);
+            if (p < l_end) {
+                const int n = p / g.O;
+                int o = p - n * g.O;
+                const int a = o / g.OHW;
+                const int r = o - a * g.OHW;
+                const int b = r / d.OW, c = r - b * d.OW;
+                const int id0 = a * d.SD - d.PD, ih0 = b * d.SH - d.PH, iw0 = c * d.SW - d.PW;
+                e.x = n * d.Cin * g.I + id0 * g.HW + ih0 * d.W + iw0;
+                e.y = (id0 + 64) | ((ih0 + 64) << 10);
+                e.z = n * d.Cout * g.O + o;
+                e.w = iw0;
+            }
+            ptab[buf * BK + threadIdx.x] = e;
+        }
+    };
 
     float acc[RM][RN];
 #pragma unroll
@@ -92,22 +114,39 @@ __global__ void __launch_bounds__(256) conv_igemm_kernel(Geo g, const float* __r
 #pragma unroll
         for (int v = 0; v < RN; ++v) acc[u][v] = 0.f;
 
-    for (int l0 = l_begin; l0 < l_end; l0 += BK) {
+    if (MODE == WGRAD) {
+        fill_ptab(l_begin, 0);
+        __syncthreads();
+    }
+    int iter = 0;
+    for (int l0 = l_begin; l0 < l_end; l0 += BK, ++iter) {
+        if (MODE != WGRAD && (iter % (LT / BK)) == 0) {
+            // decode LT reduction indices starting at l0 (the previous iteration ended with a barrier)
+            const int gl = l0 + threadIdx.x;
+            int4 e = make_int4(0, 0, 0, 0);
+            if (gl < l_end) {
+                const int ch = gl / g.KV, tap = gl - ch * g.KV;
+                const int kd = tap / g.KHW, r = tap - kd * g.KHW;
+                const int kh = r / d.KW, kw = r - kh * d.KW;
+                e.x = (MODE == FWD) ? ch * g.I + kd * g.HW + kh * d.W + kw : ch * g.O;
+                e.y = kd | (kh << 8) | (kw << 16);
+                e.z = ch * d.Cin * g.KV + tap;          // DGRAD: weight offset of (co, cin 0, tap)
+            }
+            ltab[threadIdx.x] = e;
+            __syncthreads();
+        }
+        const int tl = (iter % (LT / BK)) * BK;          // offset of this iteration inside the table window
         // ---------------- A tile
         if (MODE == WGRAD) {
-            // A(i = cout, l = position) = dy[(n*Cout + i)*O + o]: position-fastest mapping
+            // A(i = cout, l = position) = dy[n, i, o]
 #pragma unroll
             for (int q = 0; q < A_PER; ++q) {
                 const int e = threadIdx.x + q * 256;
                 if (TM * BK < 256 && e >= TM * BK) break;
                 const int l = e % BK, r = e / BK;
-                const int p = l0 + l, i = i0 + r;
-                float v = 0.f;
-                if (p < l_end && i < g.Mdim) {
-                    const int n = p / g.O, o = p - n * g.O;
-                    v = __ldg(wgt_or_dy + ((size_t)n * d.Cout + i) * g.O + o);
-                }
-                As[l][r] = v;
+                const int i = i0 + r;
+                const int4 pe = ptab[(iter & 1) * BK + l];
+                As[l][r] = (pe.z >= 0 && i < g.Mdim) ? __ldg(wgt_or_dy + (size_t)pe.z + (size_t)i * g.O) : 0.f;
             }
         } else {
 #pragma unroll
@@ -115,11 +154,20 @@ __global__ void __launch_bounds__(256) conv_igemm_kernel(Geo g, const float* __r
                 const int e = threadIdx.x + q * 256;
                 if (TM * BK < 256 && e >= TM * BK) break;
                 const int r = e % TM, l = e / TM;       // r == threadIdx.x % TM for every q (256 % TM == 0)
-                const int gl = l0 + l;
                 float v = 0.f;
-                if (pvalid && gl < l_end) {
-                    const int ch = gl / g.KV, tap = gl - ch * g.KV;
-                    v = gather<MODE>(g, act, pn, pa, pb, pc, ch, tap);
+                if (pvalid && l0 + l < l_end) {
+                    const int4 le = ltab[tl + l];
+                    const int kd = le.y & 255, kh = (le.y >> 8) & 255, kw = le.y >> 16;
+                    if (MODE == FWD) {
+                        if ((unsigned)(p_a + kd) < (unsigned)d.D && (unsigned)(p_b + kh) < (unsigned)d.H &&
+                            (unsigned)(p_c + kw) < (unsigned)d.W)
+                            v = __ldg(act + (p_base + le.x));
+                    } else {
+                        int od, oh, ow;
+                        if (div_stride(p_a - kd, d.SD, od) && div_stride(p_b - kh, d.SH, oh) && div_stride(p_c - kw, d.SW, ow) &&
+                            od < d.OD && oh < d.OH && ow < d.OW)
+                            v = __ldg(act + (p_base + le.x + od * g.OHW + oh * d.OW + ow));
+                    }
                 }
                 As[l][r] = v;
             }
@@ -144,8 +192,7 @@ __global__ void __launch_bounds__(256) conv_igemm_kernel(Geo g, const float* __r
                 const int gl = l0 + l, j = j0 + c;
                 float v = 0.f;
                 if (gl < l_end && j < g.Ndim) {
-                    const int co = gl / g.KV, tap = gl - co * g.KV;
-                    v = __ldg(wgt_or_dy + ((size_t)co * d.Cin + j) * g.KV + tap);
+                    v = __ldg(wgt_or_dy + (size_t)ltab[tl + l].z + (size_t)j * g.KV);
                 }
                 Bs[l][c] = v;
             }
@@ -156,18 +203,16 @@ __global__ void __launch_bounds__(256) conv_igemm_kernel(Geo g, const float* __r
                 const int e = threadIdx.x + q * 256;
                 if (TN * BK < 256 && e >= TN * BK) break;
                 const int c = e % TN, l = e / TN;
-                const int p = l0 + l;
+                const int4 pe = ptab[(iter & 1) * BK + l];
                 float v = 0.f;
-                if (wvalid && p < l_end) {
-                    const int n = p / g.O;
-                    int o = p - n * g.O;
-                    const int a = o / g.OHW;
-                    o -= a * g.OHW;
-                    const int b = o / d.OW, cc = o - b * d.OW;
-                    v = gather<FWD>(g, act, n, a, b, cc, wci, wtap);
+                if (wvalid && pe.z >= 0) {
+                    const int id = (pe.y & 1023) - 64 + w_kd, ih = (pe.y >> 10) - 64 + w_kh, iw = pe.w + w_kw;
+                    if ((unsigned)id < (unsigned)d.D && (unsigned)ih < (unsigned)d.H && (unsigned)iw < (unsigned)d.W)
+                        v = __ldg(act + (pe.x + w_off));
                 }
                 Bs[l][c] = v;
             }
+            fill_ptab(l0 + BK, (iter + 1) & 1);          // next iteration's positions (other buffer)
         }
         __syncthreads();
 #pragma unroll
@@ -236,7 +281,10 @@ int check_desc(const maavss_conv_desc* d, const char* who) {
                          (d->OW - 1) * d->SW - d->PW + d->KW - 1 < d->W + d->PW + d->SW,
                      "%s: output dims inconsistent with input/kernel/stride/padding", who);
     const long long pos = (long long)d->N * (d->OD * (long long)d->OH * d->OW), ipos = (long long)d->N * (d->D * (long long)d->H * d->W);
-    MAAVSS_CHECK_ARG(pos < (1LL << 31) && ipos < (1LL << 31), "%s: more than 2^31 positions", who);
+    MAAVSS_CHECK_ARG(pos * d->Cout < (1LL << 31) && ipos * d->Cin < (1LL << 31), "%s: tensors of 2^31 elements or more are not supported", who);
+    MAAVSS_CHECK_ARG(d->KD < 256 && d->KH < 256 && d->KW < 256 && d->PD < 64 && d->PH < 64 && (long long)d->OD * d->SD < 900 &&
+                         (long long)d->OH * d->SH < (1 << 20),
+                     "%s: geometry outside the packed-index range", who);
     return MAAVSS_OK;
 }
 

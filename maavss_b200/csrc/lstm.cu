@@ -53,48 +53,82 @@ __global__ void __launch_bounds__(128) lstm_step_fwd_kernel(const float* __restr
     }
 }
 
-// grid (ceil(H/256), B, 2): thread (b, j).  dh = dy + dgates[t_next] w_hh (coalesced over j), then the gate gradients.
+// Backward step.  grid (H/32, 2, ceil(B/16)), 256 threads = 32 hidden units j x 8 splits of the 4H gate rows.
+// dh[b, j] = dy[b, t, j] + sum_k dgates[b, t_next, k] w_hh[k, j]: every w_hh element is read once per CTA column
+// (coalesced over j), the 16-batch chunk of dgates(t_next) sits transposed in shared memory ([k][b], float4
+// broadcast reads), the 8 partial sums meet in shared memory, then 2 (b, j) cells per thread finish the gate gradients.
+constexpr int LB = 16;   // batch rows per chunk
 __global__ void __launch_bounds__(256) lstm_step_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ gates,
                                                             const float* __restrict__ cells, const float* __restrict__ w0,
                                                             const float* __restrict__ w1, float* __restrict__ dgates,
                                                             float* __restrict__ dcell, int B, int T, int H, int step) {
-    extern __shared__ float dgn[];   // [4H] gate gradients of the recurrence's next step for this b
-    const int b = blockIdx.y, dir = blockIdx.z;
-    const int j = blockIdx.x * 256 + threadIdx.x;
+    extern __shared__ __align__(16) float sm[];
+    float* dgn = sm;                        // [4H][LB]
+    float* red = sm + 4 * H * LB;           // [8][LB][32]
+    const int dir = blockIdx.y;
+    const int jl = threadIdx.x & 31, ks = threadIdx.x >> 5;
+    const int j = blockIdx.x * 32 + jl;
     const int t = dir ? T - 1 - step : step;
     const int tn = dir ? t - 1 : t + 1;   // time index processed at step + 1
     const int tp = dir ? t + 1 : t - 1;   // time index processed at step - 1
     const bool has_next = step + 1 < T;
-    if (has_next) {
-        const float* src = dgates + (((size_t)dir * B + b) * T + tn) * 4 * H;
-        for (int k = threadIdx.x; k < 4 * H; k += 256) dgn[k] = src[k];
-    }
-    __syncthreads();
-    if (j >= H) return;
-    float dh = dy[((size_t)b * T + t) * 2 * H + dir * H + j];
-    if (has_next) {
-        const float* w = (dir ? w1 : w0) + j;
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-        for (int k = 0; k < 4 * H; k += 4) {
-            s0 = fmaf(dgn[k], w[(size_t)k * H], s0);
-            s1 = fmaf(dgn[k + 1], w[(size_t)(k + 1) * H], s1);
-            s2 = fmaf(dgn[k + 2], w[(size_t)(k + 2) * H], s2);
-            s3 = fmaf(dgn[k + 3], w[(size_t)(k + 3) * H], s3);
+    const float* w = (dir ? w1 : w0);
+    const int H4 = 4 * H, kper = H4 / 8;
+    {
+        const int b0 = blockIdx.z * LB;
+        const int nb = min(LB, B - b0);
+        if (has_next) {
+            __syncthreads();
+            for (int e = threadIdx.x; e < LB * H4; e += 256) {
+                const int k = e % H4, b = e / H4;
+                dgn[k * LB + b] = b < nb ? dgates[(((size_t)dir * B + b0 + b) * T + tn) * H4 + k] : 0.f;
+            }
+            __syncthreads();
+            float acc[LB];
+#pragma unroll
+            for (int b = 0; b < LB; ++b) acc[b] = 0.f;
+            const int k0 = ks * kper;
+#pragma unroll 4
+            for (int k = k0; k < k0 + kper; ++k) {
+                const float wv = __ldg(w + (size_t)k * H + j);
+                const float4* d = reinterpret_cast<const float4*>(dgn + k * LB);
+#pragma unroll
+                for (int q = 0; q < LB / 4; ++q) {
+                    const float4 dv = d[q];
+                    acc[q * 4 + 0] = fmaf(dv.x, wv, acc[q * 4 + 0]);
+                    acc[q * 4 + 1] = fmaf(dv.y, wv, acc[q * 4 + 1]);
+                    acc[q * 4 + 2] = fmaf(dv.z, wv, acc[q * 4 + 2]);
+                    acc[q * 4 + 3] = fmaf(dv.w, wv, acc[q * 4 + 3]);
+                }
+            }
+#pragma unroll
+            for (int b = 0; b < LB; ++b) red[(ks * LB + b) * 32 + jl] = acc[b];
+            __syncthreads();
         }
-        dh += (s0 + s1) + (s2 + s3);
+        for (int e = threadIdx.x; e < nb * 32; e += 256) {
+            const int jj = e & 31, bl = e >> 5;
+            const int b = b0 + bl, jg = blockIdx.x * 32 + jj;
+            float dh = dy[((size_t)b * T + t) * 2 * H + dir * H + jg];
+            if (has_next) {
+                float s = 0.f;
+#pragma unroll
+                for (int q = 0; q < 8; ++q) s += red[(q * LB + bl) * 32 + jj];
+                dh += s;
+            }
+            const size_t gb = (((size_t)dir * B + b) * T + t) * H4;
+            const float ig = gates[gb + jg], fg = gates[gb + H + jg], gg = gates[gb + 2 * H + jg], og = gates[gb + 3 * H + jg];
+            const float c = cells[(((size_t)dir * B + b) * T + t) * H + jg];
+            const float cp = step > 0 ? cells[(((size_t)dir * B + b) * T + tp) * H + jg] : 0.f;
+            const float tc = tanhf(c);
+            float* dcp = dcell + ((size_t)dir * B + b) * H + jg;
+            const float dc = fmaf(dh * og, 1.f - tc * tc, *dcp);
+            dgates[gb + jg] = dc * gg * ig * (1.f - ig);
+            dgates[gb + H + jg] = dc * cp * fg * (1.f - fg);
+            dgates[gb + 2 * H + jg] = dc * ig * (1.f - gg * gg);
+            dgates[gb + 3 * H + jg] = dh * tc * og * (1.f - og);
+            *dcp = dc * fg;
+        }
     }
-    const size_t gb = (((size_t)dir * B + b) * T + t) * 4 * H;
-    const float ig = gates[gb + j], fg = gates[gb + H + j], gg = gates[gb + 2 * H + j], og = gates[gb + 3 * H + j];
-    const float c = cells[(((size_t)dir * B + b) * T + t) * H + j];
-    const float cp = step > 0 ? cells[(((size_t)dir * B + b) * T + tp) * H + j] : 0.f;
-    const float tc = tanhf(c);
-    float* dcp = dcell + ((size_t)dir * B + b) * H + j;
-    const float dc = fmaf(dh * og, 1.f - tc * tc, *dcp);
-    dgates[gb + j] = dc * gg * ig * (1.f - ig);
-    dgates[gb + H + j] = dc * cp * fg * (1.f - fg);
-    dgates[gb + 2 * H + j] = dc * ig * (1.f - gg * gg);
-    dgates[gb + 3 * H + j] = dh * tc * og * (1.f - og);
-    *dcp = dc * fg;
 }
 
 }  // namespace
@@ -123,10 +157,17 @@ extern "C" int maavss_lstm_step_bwd(const float* dy, const float* gates, const f
                                     void* stream) {
     if (B == 0 || T == 0) return MAAVSS_OK;
     MAAVSS_CHECK_ARG(dy && gates && cells && w_hh_fwd && w_hh_rev && dgates && dcell, "lstm_step_bwd: null argument");
-    MAAVSS_CHECK_ARG(step >= 0 && step < T && B <= 65535 && H <= 2048, "lstm_step_bwd: bad step/batch");
-    dim3 grid(ceil_div(H, 256), B, 2);
-    lstm_step_bwd_kernel<<<grid, 256, sizeof(float) * 4 * H, (cudaStream_t)stream>>>(dy, gates, cells, w_hh_fwd, w_hh_rev, dgates,
-                                                                                    dcell, B, T, H, step);
+    MAAVSS_CHECK_ARG(step >= 0 && step < T, "lstm_step_bwd: bad step");
+    MAAVSS_CHECK_ARG(H % 32 == 0 && H >= 32 && H <= 512, "lstm_step_bwd: H=%d must be a multiple of 32 in [32, 512]", H);
+    dim3 grid(H / 32, 2, ceil_div(B, LB));
+    const size_t smem = sizeof(float) * (4 * H * LB + 8 * LB * 32);
+    static size_t smem_set = 0;
+    if (smem > 48 * 1024 && smem > smem_set) {
+        MAAVSS_CUDA(cudaFuncSetAttribute(lstm_step_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        smem_set = smem;
+    }
+    lstm_step_bwd_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(dy, gates, cells, w_hh_fwd, w_hh_rev, dgates, dcell, B, T, H,
+                                                                   step);
     MAAVSS_LAUNCH_CHECK();
     return MAAVSS_OK;
 }

@@ -162,6 +162,151 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(const float* _
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Grouped, two-launch BatchNorm: the batch is G independent groups of N/G samples with their own statistics (the
+// num_seq accumulation windows of one optimizer step batched into one pass, train.py:136-159: the weights do not
+// change between them).  Launch 1 = partial sums per (group, channel, split); launch 2 = apply, every CTA re-deriving
+// its (group, channel) statistics from the few partials (no separate finalize launch); one designated CTA per
+// channel publishes stats and applies the G running-statistics updates in window order.
+__global__ void __launch_bounds__(kBnThreads) bn_reduce_g_kernel(const float* __restrict__ x, int Ng, int C, long long inner,
+                                                                 double* __restrict__ partial) {
+    const int c = blockIdx.y, S = gridDim.x, g = blockIdx.z;
+    const long long total = (long long)Ng * inner;
+    const long long chunk = (total + S - 1) / S;
+    const long long e0 = (long long)blockIdx.x * chunk, e1 = min(total, e0 + chunk);
+    float s1 = 0.f, s2 = 0.f;
+    for (long long e = e0 + threadIdx.x; e < e1; e += kBnThreads) {
+        const long long n = e / inner, i = e - n * inner;
+        const float v = x[((size_t)(g * Ng + n) * C + c) * inner + i];
+        s1 += v;
+        s2 = fmaf(v, v, s2);
+    }
+    block_sum2((double)s1, (double)s2, partial + (((size_t)g * C + c) * S + blockIdx.x) * 2);
+}
+
+__device__ __forceinline__ void stats_from_partial(const double* __restrict__ partial, int S, double count, float eps,
+                                                   double& mean, double& var) {
+    double s1 = 0, s2 = 0;
+    for (int s = 0; s < S; ++s) {
+        s1 += partial[2 * s];
+        s2 += partial[2 * s + 1];
+    }
+    mean = s1 / count;
+    var = s2 / count - mean * mean;
+    if (var < 0) var = 0;
+}
+
+// grid (chunks, N*C)
+__global__ void __launch_bounds__(kBnThreads) bn_apply_fused_kernel(const float* __restrict__ x, const double* __restrict__ partial,
+                                                                    int S, int Ng, int G, double count, const float* __restrict__ gamma,
+                                                                    const float* __restrict__ beta, float* __restrict__ running_mean,
+                                                                    float* __restrict__ running_var, long long* __restrict__ nbt,
+                                                                    float momentum, float eps, int C, long long inner, int act,
+                                                                    float slope, float* __restrict__ stats, float* __restrict__ y) {
+    __shared__ float sh[2];
+    const int nc = blockIdx.y, c = nc % C, n = nc / C, g = n / Ng;
+    if (threadIdx.x == 0) {
+        double mean, var;
+        stats_from_partial(partial + ((size_t)g * C + c) * S * 2, S, count, eps, mean, var);
+        sh[0] = (float)mean;
+        sh[1] = (float)(1.0 / sqrt(var + (double)eps));
+        if (blockIdx.x == 0 && n == g * Ng) {
+            stats[((size_t)g * C + c) * 2] = sh[0];
+            stats[((size_t)g * C + c) * 2 + 1] = sh[1];
+        }
+        if (blockIdx.x == 0 && n == 0) {          // one CTA per channel: running statistics, window order
+            if (running_mean) {
+                double rm = running_mean[c], rv = running_var[c];
+                for (int q = 0; q < G; ++q) {
+                    double m2, v2;
+                    stats_from_partial(partial + ((size_t)q * C + c) * S * 2, S, count, eps, m2, v2);
+                    const double unbiased = count > 1 ? v2 * count / (count - 1) : v2;
+                    // fp32 rounding after every window, like G sequential reference updates
+                    rm = (double)(float)((1.0 - momentum) * rm + momentum * m2);
+                    rv = (double)(float)((1.0 - momentum) * rv + momentum * unbiased);
+                }
+                running_mean[c] = (float)rm;
+                running_var[c] = (float)rv;
+            }
+            if (c == 0 && nbt) nbt[0] += G;
+        }
+    }
+    __syncthreads();
+    const float mean = sh[0], invstd = sh[1];
+    const float ga = gamma ? gamma[c] : 1.f, be = beta ? beta[c] : 0.f;
+    const float* xp = x + (size_t)nc * inner;
+    float* yp = y + (size_t)nc * inner;
+    for (long long i = (long long)blockIdx.x * kBnThreads + threadIdx.x; i < inner; i += (long long)gridDim.x * kBnThreads)
+        yp[i] = act_apply(fmaf((xp[i] - mean) * invstd, ga, be), act, slope);
+}
+
+__global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_g_kernel(const float* __restrict__ dy, const float* __restrict__ y,
+                                                                     const float* __restrict__ x, const float* __restrict__ stats,
+                                                                     int Ng, int C, long long inner, int act, float slope,
+                                                                     double* __restrict__ partial) {
+    const int c = blockIdx.y, S = gridDim.x, g = blockIdx.z;
+    const float mean = stats[((size_t)g * C + c) * 2], invstd = stats[((size_t)g * C + c) * 2 + 1];
+    const long long total = (long long)Ng * inner;
+    const long long chunk = (total + S - 1) / S;
+    const long long e0 = (long long)blockIdx.x * chunk, e1 = min(total, e0 + chunk);
+    float s1 = 0.f, s2 = 0.f;
+    for (long long e = e0 + threadIdx.x; e < e1; e += kBnThreads) {
+        const long long n = e / inner, i = e - n * inner;
+        const size_t q = ((size_t)(g * Ng + n) * C + c) * inner + i;
+        const float dz = dy[q] * act_grad(y[q], act, slope);
+        s1 += dz;
+        s2 = fmaf(dz, (x[q] - mean) * invstd, s2);
+    }
+    block_sum2((double)s1, (double)s2, partial + (((size_t)g * C + c) * S + blockIdx.x) * 2);
+}
+
+__global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_fused_kernel(const float* __restrict__ dy, const float* __restrict__ y,
+                                                                        const float* __restrict__ x, const float* __restrict__ stats,
+                                                                        const float* __restrict__ gamma, const double* __restrict__ partial,
+                                                                        const double* __restrict__ partial_local, int S, int Ng, int G,
+                                                                        double count, int C, long long inner, int act,
+                                                                        float slope, float* __restrict__ dgamma,
+                                                                        float* __restrict__ dbeta, int accumulate, float* __restrict__ dx) {
+    __shared__ float sh[2];
+    const int nc = blockIdx.y, c = nc % C, n = nc / C, g = n / Ng;
+    if (threadIdx.x == 0) {
+        double s1 = 0, s2 = 0;
+        const double* pp = partial + ((size_t)g * C + c) * S * 2;
+        for (int s = 0; s < S; ++s) {
+            s1 += pp[2 * s];
+            s2 += pp[2 * s + 1];
+        }
+        sh[0] = (float)(s1 / count);
+        sh[1] = (float)(s2 / count);
+        if (blockIdx.x == 0 && n == 0 && (dgamma || dbeta)) {
+            double t1 = 0, t2 = 0;
+            for (int q = 0; q < G; ++q) {            // window order, fp32 accumulation like G sequential backward passes
+                double a1 = 0, a2 = 0;
+                const double* pq = partial_local + ((size_t)q * C + c) * S * 2;
+                for (int s = 0; s < S; ++s) {
+                    a1 += pq[2 * s];
+                    a2 += pq[2 * s + 1];
+                }
+                t1 = (double)(float)(t1 + (float)a1);
+                t2 = (double)(float)(t2 + (float)a2);
+            }
+            if (dgamma) dgamma[c] = accumulate ? dgamma[c] + (float)t2 : (float)t2;
+            if (dbeta) dbeta[c] = accumulate ? dbeta[c] + (float)t1 : (float)t1;
+        }
+    }
+    __syncthreads();
+    if (!dx) return;
+    const float mean = stats[((size_t)g * C + c) * 2], invstd = stats[((size_t)g * C + c) * 2 + 1];
+    const float scale = (gamma ? gamma[c] : 1.f) * invstd;
+    const float c0 = sh[0], c1 = sh[1];
+    const size_t base = (size_t)nc * inner;
+    for (long long i = (long long)blockIdx.x * kBnThreads + threadIdx.x; i < inner; i += (long long)gridDim.x * kBnThreads) {
+        const float dz = dy[base + i] * act_grad(y[base + i], act, slope);
+        const float xh = (x[base + i] - mean) * invstd;
+        dx[base + i] = scale * (dz - c0 - xh * c1);
+    }
+}
+
 __global__ void act_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, long long n, int act, float slope) {
     for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < n; q += (long long)gridDim.x * blockDim.x)
         y[q] = act_apply(x[q], act, slope);
@@ -251,6 +396,58 @@ extern "C" int maavss_bn_bwd_apply(const float* dy, const float* y, const float*
     MAAVSS_CHECK_ARG((long long)N * C <= 65535, "bn_bwd_apply: N*C > 65535");
     dim3 grid(inner_chunks(inner, (long long)N * C), N * C);
     bn_bwd_apply_kernel<<<grid, kBnThreads, 0, (cudaStream_t)stream>>>(dy, y, x, stats, gamma, coef, C, inner, act, slope, dx);
+    MAAVSS_LAUNCH_CHECK();
+    return MAAVSS_OK;
+}
+
+extern "C" int maavss_bn_reduce_grouped(const float* x, int N, int C, long long inner, int groups, double* partial, void* stream) {
+    if ((long long)N * C * inner == 0) return MAAVSS_OK;
+    MAAVSS_CHECK_ARG(x && partial && C > 0 && C <= 65535, "bn_reduce_grouped: bad argument");
+    MAAVSS_CHECK_ARG(groups >= 1 && groups <= 65535 && N % groups == 0, "bn_reduce_grouped: batch %d is not a multiple of %d groups", N, groups);
+    const int Ng = N / groups, S = maavss_bn_splits(Ng, C, inner);
+    bn_reduce_g_kernel<<<dim3(S, C, groups), kBnThreads, 0, (cudaStream_t)stream>>>(x, Ng, C, inner, partial);
+    MAAVSS_LAUNCH_CHECK();
+    return MAAVSS_OK;
+}
+
+extern "C" int maavss_bn_apply_grouped(const float* x, const double* partial, int N, int C, long long inner, int groups, double count,
+                                       const float* gamma, const float* beta, float* running_mean, float* running_var,
+                                       long long* num_batches_tracked, float momentum, float eps, int act, float slope, float* stats,
+                                       float* y, void* stream) {
+    if ((long long)N * C * inner == 0) return MAAVSS_OK;
+    MAAVSS_CHECK_ARG(x && partial && stats && y && C > 0, "bn_apply_grouped: bad argument");
+    MAAVSS_CHECK_ARG(groups >= 1 && N % groups == 0 && (long long)N * C <= 65535 && count > 0, "bn_apply_grouped: bad batch / groups");
+    const int Ng = N / groups, S = maavss_bn_splits(Ng, C, inner);
+    dim3 grid(inner_chunks(inner, (long long)N * C), N * C);
+    bn_apply_fused_kernel<<<grid, kBnThreads, 0, (cudaStream_t)stream>>>(x, partial, S, Ng, groups, count, gamma, beta, running_mean,
+                                                                        running_var, num_batches_tracked, momentum, eps, C, inner,
+                                                                        act, slope, stats, y);
+    MAAVSS_LAUNCH_CHECK();
+    return MAAVSS_OK;
+}
+
+extern "C" int maavss_bn_bwd_reduce_grouped(const float* dy, const float* y, const float* x, const float* stats, int N, int C,
+                                            long long inner, int groups, int act, float slope, double* partial, void* stream) {
+    if ((long long)N * C * inner == 0) return MAAVSS_OK;
+    MAAVSS_CHECK_ARG(dy && y && x && stats && partial && C > 0 && C <= 65535, "bn_bwd_reduce_grouped: bad argument");
+    MAAVSS_CHECK_ARG(groups >= 1 && groups <= 65535 && N % groups == 0, "bn_bwd_reduce_grouped: bad batch / groups");
+    const int Ng = N / groups, S = maavss_bn_splits(Ng, C, inner);
+    bn_bwd_reduce_g_kernel<<<dim3(S, C, groups), kBnThreads, 0, (cudaStream_t)stream>>>(dy, y, x, stats, Ng, C, inner, act, slope, partial);
+    MAAVSS_LAUNCH_CHECK();
+    return MAAVSS_OK;
+}
+
+extern "C" int maavss_bn_bwd_apply_grouped(const float* dy, const float* y, const float* x, const float* stats, const float* gamma,
+                                           const double* partial, const double* partial_local, int N, int C, long long inner,
+                                           int groups, double count, int act, float slope, float* dgamma, float* dbeta, int accumulate,
+                                           float* dx, void* stream) {
+    if ((long long)N * C * inner == 0) return MAAVSS_OK;
+    MAAVSS_CHECK_ARG(dy && y && x && stats && partial && partial_local && C > 0, "bn_bwd_apply_grouped: bad argument");
+    MAAVSS_CHECK_ARG(groups >= 1 && N % groups == 0 && (long long)N * C <= 65535 && count > 0, "bn_bwd_apply_grouped: bad batch / groups");
+    const int Ng = N / groups, S = maavss_bn_splits(Ng, C, inner);
+    dim3 grid(inner_chunks(inner, (long long)N * C), N * C);
+    bn_bwd_apply_fused_kernel<<<grid, kBnThreads, 0, (cudaStream_t)stream>>>(dy, y, x, stats, gamma, partial, partial_local, S, Ng, groups,
+                                                                            count, C, inner, act, slope, dgamma, dbeta, accumulate, dx);
     MAAVSS_LAUNCH_CHECK();
     return MAAVSS_OK;
 }

@@ -16,6 +16,8 @@ ACT_NONE, ACT_TANH, ACT_LEAKY, ACT_SIGMOID = 0, 1, 2, 3
 # data-parallel context: set by parallel.init(); when not None, train-mode BatchNorm statistics are all-reduced
 # over this process group so that N ranks reproduce the single-process global-batch result.
 SYNC_BN_GROUP = None
+# number of independent sub-batches (accumulation windows batched by train_step) a train-mode BatchNorm normalises separately
+BN_GROUPS = 1
 
 
 class ConvDesc(ctypes.Structure):
@@ -146,7 +148,11 @@ def _allreduce_partial(partial):
 
 
 class BNActFn(torch.autograd.Function):
-    """act(BatchNorm(x)) with batch statistics in training (running stats in eval), any channels-first rank."""
+    """act(BatchNorm(x)) with batch statistics in training (running stats in eval), any channels-first rank.
+
+    Training runs the two-launch grouped kernels: `BN_GROUPS` consecutive sub-batches of the batch dimension are
+    normalised independently (the accumulation windows of one optimizer step batched by train_step); with a
+    data-parallel group set, the (groups, C, S, 2) partial sums are all-reduced between the two launches."""
 
     @staticmethod
     def forward(ctx, x, gamma, beta, running_mean, running_var, nbt, training, momentum, eps, act, slope):
@@ -154,64 +160,73 @@ class BNActFn(torch.autograd.Function):
         N, C = x.shape[0], x.shape[1]
         inner = x[0, 0].numel() if N else 0
         L = lib()
-        stats = torch.empty(C, 2, device=x.device, dtype=torch.float32)
         use_batch = training or running_mean is None
-        S, world = 1, 1
+        y = torch.empty_like(x)
         if use_batch:
-            S = L.maavss_bn_splits(N, C, inner)
-            partial = torch.empty(C, S, 2, device=x.device, dtype=torch.float64)
-            check(L.maavss_bn_reduce(fptr(x), N, C, inner, dptr(partial), stream_ptr()))
+            G = BN_GROUPS if (training and N % max(BN_GROUPS, 1) == 0) else 1
+            S = L.maavss_bn_splits(N // G, C, inner)
+            partial = torch.empty(G, C, S, 2, device=x.device, dtype=torch.float64)
+            stats = torch.empty(G, C, 2, device=x.device, dtype=torch.float32)
+            check(L.maavss_bn_reduce_grouped(fptr(x), N, C, inner, G, dptr(partial), stream_ptr()))
+            world = 1
             if SYNC_BN_GROUP is not None and training:
                 world = _allreduce_partial(partial)
-            count = float(N * inner * world)
-            check(L.maavss_bn_finalize(dptr(partial), S, C, count, eps, momentum if momentum is not None else 0.1,
-                                       _opt(running_mean) if training else _null(), _opt(running_var) if training else _null(),
-                                       dptr(nbt) if (nbt is not None and training) else _null(), 0, fptr(stats), stream_ptr()))
+            count = float((N // G) * inner * world)
+            check(L.maavss_bn_apply_grouped(fptr(x), dptr(partial), N, C, inner, G, count, _opt(gamma), _opt(beta),
+                                            _opt(running_mean) if training else _null(), _opt(running_var) if training else _null(),
+                                            dptr(nbt) if (nbt is not None and training) else _null(),
+                                            momentum if momentum is not None else 0.1, eps, act, slope, fptr(stats), fptr(y),
+                                            stream_ptr()))
         else:
+            G, world = 1, 1
+            stats = torch.empty(1, C, 2, device=x.device, dtype=torch.float32)
             check(L.maavss_bn_finalize(_null(), 0, C, 1.0, eps, 0.0, fptr(running_mean), fptr(running_var), _null(), 1,
                                        fptr(stats), stream_ptr()))
-        y = torch.empty_like(x)
-        check(L.maavss_bn_apply_act(fptr(x), fptr(stats), _opt(gamma), _opt(beta), N, C, inner, act, slope, fptr(y), stream_ptr()))
-        ctx.cfg = (N, C, inner, act, slope, use_batch, world)
+            check(L.maavss_bn_apply_act(fptr(x), fptr(stats), _opt(gamma), _opt(beta), N, C, inner, act, slope, fptr(y), stream_ptr()))
+        ctx.cfg = (N, C, inner, act, slope, use_batch, world, G)
         ctx.save_for_backward(x, y, stats, gamma, beta)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         x, y, stats, gamma, beta = ctx.saved_tensors
-        N, C, inner, act, slope, use_batch, world = ctx.cfg
+        N, C, inner, act, slope, use_batch, world, G = ctx.cfg
         dy = dy.contiguous()
         L = lib()
-        S = L.maavss_bn_splits(N, C, inner)
-        partial = torch.empty(C, S, 2, device=x.device, dtype=torch.float64)
-        check(L.maavss_bn_bwd_reduce(fptr(dy), fptr(y), fptr(x), fptr(stats), N, C, inner, act, slope, dptr(partial), stream_ptr()))
         gg_t, gg_acc, gg = _grad_slot(gamma, gamma is not None and ctx.needs_input_grad[1])
         gb_t, gb_acc, gb = _grad_slot(beta, beta is not None and ctx.needs_input_grad[2])
-        if gg_t is not None and gb_t is not None and gg_acc != gb_acc:      # keep one accumulate flag for the fused finalize
-            gb_t, gb_acc, gb = torch.empty_like(beta), 0, None
+        if gg_t is not None and gb_t is not None and gg_acc != gb_acc:      # keep one accumulate flag for the fused kernel
+            gb_t, gb_acc = torch.empty_like(beta), 0
             gb = gb_t
             if gg_acc:
                 gg_t, gg_acc = torch.empty_like(gamma), 0
                 gg = gg_t
-        if world > 1:
-            # local parameter gradients come from the LOCAL sums (they are averaged by the gradient all-reduce);
-            # the input gradient needs the GLOBAL sums.
-            local = partial.clone()
-            _allreduce_partial(partial)
-            coef = torch.empty(C, 2, device=x.device, dtype=torch.float32)
-            check(L.maavss_bn_bwd_finalize(dptr(local), S, C, float(N * inner), 0, fptr(coef), _opt(gg_t), _opt(gb_t),
-                                           gg_acc if gg_t is not None else gb_acc, stream_ptr()))
-            check(L.maavss_bn_bwd_finalize(dptr(partial), S, C, float(N * inner * world), 0, fptr(coef), _null(), _null(), 0,
-                                           stream_ptr()))
+        acc = gg_acc if gg_t is not None else gb_acc
+        dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        if use_batch:
+            S = L.maavss_bn_splits(N // G, C, inner)
+            partial = torch.empty(G, C, S, 2, device=x.device, dtype=torch.float64)
+            check(L.maavss_bn_bwd_reduce_grouped(fptr(dy), fptr(y), fptr(x), fptr(stats), N, C, inner, G, act, slope, dptr(partial),
+                                                 stream_ptr()))
+            local = partial
+            if world > 1:
+                # parameter gradients come from the LOCAL sums (the gradient all-reduce averages them); the input
+                # gradient needs the GLOBAL sums.
+                local = partial.clone()
+                _allreduce_partial(partial)
+            check(L.maavss_bn_bwd_apply_grouped(fptr(dy), fptr(y), fptr(x), fptr(stats), _opt(gamma), dptr(partial), dptr(local), N, C,
+                                                inner, G, float((N // G) * inner * world), act, slope, _opt(gg_t), _opt(gb_t), acc,
+                                                fptr(dx) if dx is not None else _null(), stream_ptr()))
         else:
+            S = L.maavss_bn_splits(N, C, inner)
+            partial = torch.empty(C, S, 2, device=x.device, dtype=torch.float64)
+            check(L.maavss_bn_bwd_reduce(fptr(dy), fptr(y), fptr(x), fptr(stats), N, C, inner, act, slope, dptr(partial), stream_ptr()))
             coef = torch.empty(C, 2, device=x.device, dtype=torch.float32)
-            check(L.maavss_bn_bwd_finalize(dptr(partial), S, C, float(N * inner), 0 if use_batch else 1, fptr(coef), _opt(gg_t),
-                                           _opt(gb_t), gg_acc if gg_t is not None else gb_acc, stream_ptr()))
-        dx = None
-        if ctx.needs_input_grad[0]:
-            dx = torch.empty_like(x)
-            check(L.maavss_bn_bwd_apply(fptr(dy), fptr(y), fptr(x), fptr(stats), _opt(gamma), fptr(coef), N, C, inner, act, slope,
-                                        fptr(dx), stream_ptr()))
+            check(L.maavss_bn_bwd_finalize(dptr(partial), S, C, float(N * inner), 1, fptr(coef), _opt(gg_t), _opt(gb_t), acc,
+                                           stream_ptr()))
+            if dx is not None:
+                check(L.maavss_bn_bwd_apply(fptr(dy), fptr(y), fptr(x), fptr(stats), _opt(gamma), fptr(coef), N, C, inner, act, slope,
+                                            fptr(dx), stream_ptr()))
         return dx, gg, gb, None, None, None, None, None, None, None, None
 
 

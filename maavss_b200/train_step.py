@@ -66,12 +66,43 @@ class _TrainStepBase:
 
 
 class FusionTrainStep(_TrainStepBase):
-    def __init__(self, model, optimizer, num_seq=4, num_frames=8, hops_per_frame=8, p_size=64, loss_coeff=0.001, **kw):
+    """batch_windows=True (default): the num_seq accumulation windows are stacked along the batch axis and run as ONE
+    forward/backward pass -- the weights are constant between them (the optimizer steps only after the last one), so
+    the result is the reference's sum of per-window gradients; train-mode BatchNorm keeps per-window statistics
+    (nn_ops.BN_GROUPS) and applies its running-statistics updates in window order.  Every weight matrix is then
+    streamed from HBM once per optimizer step instead of num_seq times and the launch count drops by num_seq."""
+
+    def __init__(self, model, optimizer, num_seq=4, num_frames=8, hops_per_frame=8, p_size=64, loss_coeff=0.001,
+                 batch_windows=True, **kw):
         super().__init__(model, optimizer, **kw)
         self.num_seq, self.num_frames, self.hpf, self.p_size, self.loss_coeff = num_seq, num_frames, hops_per_frame, p_size, loss_coeff
+        self.batch_windows = batch_windows
+
+    def _windows_batched(self, x_stft, y_stft, attn):
+        G, B = self.num_seq, x_stft.shape[0]
+        span = self.hpf * self.num_frames
+        pgram = torch.cat([phasegram_ops.video_phasegram(attn[:, :, j:j + self.num_frames], resize=(self.p_size, self.p_size))
+                           for j in range(G)], 0)
+        xa = torch.cat([x_stft[:, :, self.hpf * j:self.hpf * j + span, :] for j in range(G)], 0)
+        ya = torch.cat([y_stft[:, :, self.hpf * j:self.hpf * j + span, :] for j in range(G)], 0)
+        nn_ops.BN_GROUPS = G
+        try:
+            yh_a, yh_v, _ = self.model(xa, pgram)
+            # equal window sizes: the MSE over the stack is the mean of the per-window MSEs = sum_j (.)_j / num_seq
+            loss = nn_ops.mse_loss(yh_a, ya) + self.loss_coeff * nn_ops.mse_loss(yh_v, pgram)
+            loss.backward()
+        finally:
+            nn_ops.BN_GROUPS = 1
+        with torch.no_grad():                     # what the sequential loop reports: the last window's losses
+            a_loss = nn_ops.mse_loss(yh_a[-B:], ya[-B:])
+            v_loss = nn_ops.mse_loss(yh_v[-B:], pgram[-B:])
+            last = (a_loss + self.loss_coeff * v_loss) / G
+        return last, a_loss, v_loss
 
     def micro_steps(self, x_stft, y_stft, attn):
         """x_stft, y_stft (B, 2, hpf*(num_frames+num_seq), F); attn (B, 1, num_frames+num_seq, H, W)."""
+        if self.batch_windows:
+            return self._windows_batched(x_stft, y_stft, attn)
         loss = a_loss = v_loss = None
         for j in range(self.num_seq):
             pgram = phasegram_ops.video_phasegram(attn[:, :, j:j + self.num_frames], resize=(self.p_size, self.p_size))
