@@ -7,6 +7,8 @@
 // Twiddles come from a shared-memory table tw[q] = exp(-2*pi*i*q/(2M)), q in [0, M).
 #pragma once
 #include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
 
 __device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
 __device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
@@ -170,4 +172,75 @@ __device__ __forceinline__ void fft_forward_block(float2 (&v)[16], int i, const 
         fft_pass<M, R2, 16 * R1>(v, i, tw, buf);
     }
     __syncthreads();
+}
+
+// ------------------------------------------------------------------------------------------------
+// Table-twiddle variant.  Every twiddle a thread needs in passes >= 2 depends only on its thread
+// index i (element j = i + b*TPF is fixed), so the plan tabulates them per thread:
+//     ttab[(slot * TPF) + i],  slot = SLOT0 + b*(R-1) + (r-1)  ->  exp(-2*pi*i * r*k / (NS*R)),  k = j & (NS-1)
+// One LDS.64 per twiddle replaces the index arithmetic + cmul chains of fft_pass.
+template <int M>
+struct FftShape {
+    static constexpr int TPF = M / 16;
+    static constexpr int R1 = (M / 16 >= 16) ? 16 : (M / 16);
+    static constexpr int R2 = M / (16 * R1);
+    static constexpr int SLOTS1 = 16 - 16 / R1;
+    static constexpr int SLOTS2 = (R2 > 1) ? 16 - 16 / R2 : 0;
+    static constexpr int NSLOT = SLOTS1 + SLOTS2;
+};
+
+// Host side: fill ttab (NSLOT * TPF float2) for an M-point FFT.  M is a runtime value here so the
+// plan and the CPU emulation share it.
+static inline int fft_ttab_len(int M) {
+    const int R1 = (M / 16 >= 16) ? 16 : (M / 16), R2 = M / (16 * R1);
+    return ((16 - 16 / R1) + (R2 > 1 ? 16 - 16 / R2 : 0)) * (M / 16);
+}
+static inline void fft_build_ttab(int M, float2* ttab) {
+    const int TPF = M / 16;
+    const int R1 = (M / 16 >= 16) ? 16 : (M / 16), R2 = M / (16 * R1);
+    int slot0 = 0;
+    const int radix[2] = {R1, R2};
+    int NS = 16;
+    for (int p = 0; p < 2; ++p) {
+        const int R = radix[p];
+        if (R <= 1) break;
+        const int NB = 16 / R;
+        for (int b = 0; b < NB; ++b)
+            for (int r = 1; r < R; ++r)
+                for (int i = 0; i < TPF; ++i) {
+                    const int k = (i + b * TPF) & (NS - 1);
+                    const double ang = -2.0 * 3.14159265358979323846 * (double)(r * k) / (double)(NS * R);
+                    ttab[(slot0 + b * (R - 1) + (r - 1)) * TPF + i] = make_float2((float)cos(ang), (float)sin(ang));
+                }
+        slot0 += NB * (R - 1);
+        NS *= R;
+    }
+}
+
+// One Stockham pass with tabulated twiddles.  PAD selects the padded exchange layout (needed for
+// every pass but the last, whose scatter is already lane-contiguous) or a plain natural-order array.
+template <int M, int R, int NS, int SLOT0, bool PAD>
+__device__ __forceinline__ void fft_pass_t(const float2 (&v)[16], int i, const float2* __restrict__ ttab,
+                                           float2* __restrict__ out) {
+    constexpr int TPF = M / 16;
+    constexpr int NB = 16 / R;
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+        const int j = i + b * TPF;
+        const int k = j & (NS - 1);
+        float2 u[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) u[r] = v[b + r * NB];
+        if constexpr (NS > 1) {
+#pragma unroll
+            for (int r = 1; r < R; ++r) u[r] = cmul(u[r], ttab[(SLOT0 + b * (R - 1) + (r - 1)) * TPF + i]);
+        }
+        Dft<R>::run(u);
+        const int j0 = (j / NS) * (NS * R) + k;
+#pragma unroll
+        for (int q = 0; q < R; ++q) {
+            const int x = j0 + q * NS;
+            out[PAD ? pad_idx(x) : x] = u[q];
+        }
+    }
 }

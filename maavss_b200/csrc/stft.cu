@@ -4,7 +4,14 @@
 //        1/sqrt(sum w^2) + last-frame / Nyquist trim + (2,T,F) plane layout (+ optional mag/phase),
 //        one pass over HBM: reads 4*N bytes, writes 8*F*T bytes per clip.
 // iSTFT: Nyquist zero re-pad + Hermitian unpack + inverse FFT + sqrt(n) + window + gather-style
-//        (deterministic, atomics-free) overlap-add in shared memory + 1/sum w^2 envelope + centre trim.
+//        (deterministic, atomics-free) overlap-add in a shared-memory ring + 1/sum w^2 envelope + centre trim.
+//
+// Both kernels are instruction-issue bound before they are HBM bound (an fp32 FFT costs about as many
+// issue slots per frame as the frame's bytes cost HBM cycles), so the design minimises instructions:
+// 16 points per thread, radix-16 register butterflies, every twiddle / window value a thread needs is
+// thread-constant and read with one LDS.64 from a per-thread table, scaling is folded into the tables,
+// and a frame's TPF = n_fft/32 threads synchronise among themselves (warp sync or a named barrier),
+// never with the whole CTA in the forward kernel.
 #include <math.h>
 #include <stdlib.h>
 #include "common.cuh"
@@ -14,32 +21,85 @@
 struct maavss_stft_plan {
     int n_fft, hop;
     float2* tw;      // device, n_fft/2 entries: exp(-2*pi*i*q/n_fft)
+    float2* ttab;    // device, per-thread pass twiddles (fft_build_ttab)
     float* window;   // device, n_fft
+    float* ienv;     // device, hop entries: 1 / sum_q w^2[r + q*hop]
     double sum_w2;
     int device;
 };
 
 namespace {
 
-constexpr int kThreads = 256;
+static inline int round_up(int a, int b) { return (a + b - 1) / b * b; }
+
+template <int M>
+struct Cfg {
+    static constexpr int TPF = M / 16;
+    static constexpr int NT = (M >= 2048) ? 512 : 256;        // threads per CTA (inverse); forward uses 256
+    static constexpr int TTAB = FftShape<M>::NSLOT * TPF;       // float2 entries
+};
+
+// Synchronise the TPF threads that share one frame.
+template <int TPF>
+__device__ __forceinline__ void group_sync(int fi) {
+    if constexpr (TPF <= 32) {
+        __syncwarp();
+    } else {
+        asm volatile("bar.sync %0, %1;" ::"r"(fi + 1), "n"(TPF) : "memory");
+    }
+}
+
+// M-point forward FFT of v (elements i + m*TPF); result in natural order in buf (padded layout when
+// PADFINAL, plain otherwise).  Only the frame's own threads synchronise.
+template <int M, bool PADFINAL>
+__device__ __forceinline__ void fft_group(float2 (&v)[16], int i, int fi, const float2* __restrict__ ttab,
+                                          float2* __restrict__ buf) {
+    using S = FftShape<M>;
+    constexpr int TPF = S::TPF;
+    fft_pass_t<M, 16, 1, 0, true>(v, i, ttab, buf);
+    group_sync<TPF>(fi);
+    fft_reload<M>(v, i, buf);
+    group_sync<TPF>(fi);
+    if constexpr (S::R2 > 1) {
+        fft_pass_t<M, S::R1, 16, 0, true>(v, i, ttab, buf);
+        group_sync<TPF>(fi);
+        fft_reload<M>(v, i, buf);
+        group_sync<TPF>(fi);
+        fft_pass_t<M, S::R2, 16 * S::R1, S::SLOTS1, PADFINAL>(v, i, ttab, buf);
+    } else {
+        fft_pass_t<M, S::R1, 16, 0, PADFINAL>(v, i, ttab, buf);
+    }
+    group_sync<TPF>(fi);
+}
+
+constexpr int kFwdThreads = 256;
 
 struct StftArgs {
     const float* audio;
     float* planes;
     const float2* tw;
+    const float2* ttab;
     const float* window;
     int n_samples, hop, T_out, F_out, batches_per_cta, polar;
     float scale;
 };
 
 template <int M>
-__global__ void __launch_bounds__(kThreads) stft_fwd_kernel(StftArgs a) {
+__global__ void __launch_bounds__(kFwdThreads) stft_fwd_kernel(StftArgs a) {
     constexpr int TPF = M / 16;
-    constexpr int P = kThreads / TPF;
+    constexpr int P = kFwdThreads / TPF;
     extern __shared__ float2 smem[];
-    float2* tw = smem;
-    float2* bufs = smem + M;
-    for (int q = threadIdx.x; q < M; q += kThreads) tw[q] = a.tw[q];
+    float2* tw = smem;                       // M
+    float2* wsm = tw + M;                    // M   (window pairs, pre-scaled)
+    float2* ttab = wsm + M;                  // Cfg<M>::TTAB
+    float2* bufs = ttab + Cfg<M>::TTAB;      // P * fft_buf_len(M)
+    const float hs = 0.5f * a.scale;
+    for (int q = threadIdx.x; q < M; q += kFwdThreads) {
+        tw[q] = a.tw[q];
+        const float2 w = *reinterpret_cast<const float2*>(a.window + 2 * q);
+        wsm[q] = make_float2(w.x * hs, w.y * hs);
+    }
+    for (int q = threadIdx.x; q < Cfg<M>::TTAB; q += kFwdThreads) ttab[q] = a.ttab[q];
     const int fi = threadIdx.x / TPF, i = threadIdx.x % TPF;
     float2* buf = bufs + fi * fft_buf_len(M);
     const float* clip = a.audio + (size_t)blockIdx.y * a.n_samples;
@@ -52,17 +112,17 @@ __global__ void __launch_bounds__(kThreads) stft_fwd_kernel(StftArgs a) {
         const bool active = t < a.T_out;
         float2 v[16];
         if (active) {
-            stft_load_frame<M>(v, i, clip, a.window, t, a.hop, a.n_samples);
+            stft_load_frame<M>(v, i, clip, wsm, t, a.hop, a.n_samples);
         } else {
 #pragma unroll
             for (int m = 0; m < 16; ++m) v[m] = make_float2(0.f, 0.f);
         }
-        fft_forward_block<M>(v, i, tw, buf);
+        fft_group<M, true>(v, i, fi, ttab, buf);
         if (active) {
             float* row0 = out + (size_t)t * a.F_out;
-            stft_post_frame<M>(i, buf, tw, row0, row0 + (size_t)a.T_out * a.F_out, a.F_out, a.scale, a.polar);
+            stft_post_frame<M>(i, buf, tw, row0, row0 + (size_t)a.T_out * a.F_out, a.F_out, a.polar);
         }
-        __syncthreads();
+        group_sync<TPF>(fi);
     }
 }
 
@@ -70,70 +130,77 @@ struct IstftArgs {
     const float* planes;
     float* audio;
     const float2* tw;
+    const float2* ttab;
     const float* window;
+    const float* ienv;
     int hop, T, F_in, G, polar, out_len;
     float scale;
 };
 
-template <int M>
-__global__ void __launch_bounds__(kThreads) istft_kernel(IstftArgs a) {
+// One CTA owns G hop-slots of one clip: padded positions [t_a*hop, t_b*hop).  It walks the frames
+// [t_a - (N-1)/hop, min(t_b, T)) in batches of P, inverse-transforms each batch into shared memory
+// and folds it into the overlap-add ring (istft_gather_elem).
+template <int M, int V>
+__global__ void __launch_bounds__(Cfg<M>::NT) istft_kernel(IstftArgs a) {
     constexpr int TPF = M / 16;
-    constexpr int P = kThreads / TPF;
+    constexpr int NT = Cfg<M>::NT;
+    constexpr int P = NT / TPF;
     constexpr int N = 2 * M;
+    constexpr int FS = 2 * fft_buf_len(M);          // floats between frames
     extern __shared__ float2 smem[];
-    float2* tw = smem;
-    float2* bufs = smem + M;
-    float* acc = reinterpret_cast<float*>(bufs + P * fft_buf_len(M));
+    float2* tw = smem;                               // M
+    float2* ttab = tw + M;                           // TTAB
+    float2* bufs = ttab + Cfg<M>::TTAB;              // P * fft_buf_len(M)
+    float* wg = reinterpret_cast<float*>(bufs + P * fft_buf_len(M));   // N
+    float* acc = wg + N;                             // L
     const int tid = threadIdx.x;
     const int fi = tid / TPF, i = tid % TPF;
     const int hop = a.hop;
-    const int s0 = blockIdx.x * a.G * hop;
-    const int S_out = min(a.G * hop, a.out_len - s0);
-    const int u0 = s0 + M;  // padded coordinate of the first output sample of this strip
-    int t_lo = (u0 - N + 1 > 0) ? (u0 - N + 1 + hop - 1) / hop : 0;
-    int t_hi = min(a.T - 1, (u0 + S_out - 1) / hop);
-    for (int q = tid; q < M; q += kThreads) tw[q] = a.tw[q];
-    for (int q = tid; q < S_out; q += kThreads) acc[q] = 0.f;
+    IstftGather c;
+    c.hop = hop; c.N = N; c.M = M; c.T = a.T;
+    c.PH = P * hop;
+    c.L = (P - 1) * hop + N;
+    c.frame_stride = FS;
+    c.inv_hop = 1.0f / (float)hop;
+    const int t_a = blockIdx.x * a.G, t_b = t_a + a.G;
+    c.own_lo = max(M, t_a * hop);
+    c.own_hi = min(M + a.out_len, t_b * hop);
+    const int t_lim = min(t_b, a.T);                 // frames >= t_lim are not needed / do not exist
+    const int t_start = max(0, t_a - (N - 1) / hop);
+    for (int q = tid; q < M; q += NT) tw[q] = a.tw[q];
+    for (int q = tid; q < Cfg<M>::TTAB; q += NT) ttab[q] = a.ttab[q];
+    const float sc = 0.5f * a.scale;
+    for (int q = tid; q < N; q += NT) wg[q] = a.window[q] * ((q & 1) ? -sc : sc);
+    for (int q = tid; q < c.L; q += NT) acc[q] = 0.f;
+    const float inv_scale2 = 1.0f / (sc * sc);
     const float* in0 = a.planes + (size_t)blockIdx.y * 2 * a.T * a.F_in;
     const float* in1 = in0 + (size_t)a.T * a.F_in;
+    float* out_clip = a.audio + (size_t)blockIdx.y * a.out_len;
+    float2* buf = bufs + fi * fft_buf_len(M);
+    c.off = 0;
     __syncthreads();
-    for (int tb = t_lo; tb <= t_hi; tb += P) {
+    for (int tb = t_start; tb * hop < c.own_hi; tb += P) {
         const int t = tb + fi;
-        const int t_last = min(tb + P - 1, t_hi);
-        float2 v[16];
-        if (t <= t_hi) {
-            istft_load_frame<M>(v, i, in0 + (size_t)t * a.F_in, in1 + (size_t)t * a.F_in, a.F_in, tw, a.polar);
-        } else {
+        // a warp (or barrier group) whose frames are all beyond t_lim skips the transform altogether
+        const int t_group0 = (TPF >= 32) ? t : tb + (tid & ~31) / TPF;
+        if (t_group0 < t_lim) {
+            float2 v[16];
+            if (t < t_lim) {
+                istft_load_frame<M>(v, i, in0 + (size_t)t * a.F_in, in1 + (size_t)t * a.F_in, a.F_in, tw, a.polar);
+            } else {
 #pragma unroll
-            for (int m = 0; m < 16; ++m) v[m] = make_float2(0.f, 0.f);
-        }
-        fft_forward_block<M>(v, i, tw, bufs + fi * fft_buf_len(M));
-        const int lo = max(u0, tb * hop);
-        const int hi = min(u0 + S_out, t_last * hop + N);
-        for (int u = lo + tid; u < hi; u += kThreads) {
-            int tf = (u - N + 1 > 0) ? (u - N + 1 + hop - 1) / hop : 0;
-            tf = max(tf, tb);
-            const int tl = min(t_last, u / hop);
-            float s = 0.f;
-            for (int tt = tf; tt <= tl; ++tt) {
-                const int j = u - tt * hop;
-                s += istft_frame_sample(bufs + (tt - tb) * fft_buf_len(M), j) * __ldg(a.window + j);
+                for (int m = 0; m < 16; ++m) v[m] = make_float2(0.f, 0.f);
             }
-            acc[u - u0] += s;
+            fft_group<M, false>(v, i, fi, ttab, buf);
         }
         __syncthreads();
-    }
-    float* out = a.audio + (size_t)blockIdx.y * a.out_len + s0;
-    for (int q = tid; q < S_out; q += kThreads) {
-        const int u = u0 + q;
-        const int tf = (u - N + 1 > 0) ? (u - N + 1 + hop - 1) / hop : 0;
-        const int tl = min(a.T - 1, u / hop);
-        float env = 0.f;
-        for (int tt = tf; tt <= tl; ++tt) {
-            const float w = __ldg(a.window + (u - tt * hop));
-            env = fmaf(w, w, env);
-        }
-        out[q] = acc[q] * a.scale / env;
+        c.base_u = tb * hop;
+        c.nvalid = max(0, min(P, t_lim - tb));
+        for (int e = tid; e < c.L / V; e += NT)
+            istft_gather_elem<V>(e, c, acc, reinterpret_cast<const float*>(bufs), wg, a.ienv, inv_scale2, out_clip);
+        c.off += c.PH;
+        if (c.off >= c.L) c.off -= c.L;
+        __syncthreads();
     }
 }
 
@@ -168,13 +235,32 @@ __global__ void axpy_kernel(const float* __restrict__ y, const float* __restrict
 template <int M>
 int launch_stft(const maavss_stft_plan* p, const StftArgs& a0, int batch, cudaStream_t st) {
     StftArgs a = a0;
-    constexpr int P = kThreads / (M / 16);
+    constexpr int P = kFwdThreads / (M / 16);
     const int batches = ceil_div(a.T_out, P);
-    a.batches_per_cta = ((long long)batches * batch >= 148LL * 32) ? 4 : 1;
+    // enough CTAs for ~8 waves of 3 resident CTAs per SM; each CTA amortises its table prologue over bpc batches
+    long long bpc = ceil_div((long long)batches * batch, 148LL * 3 * 8);
+    if (bpc < 1) bpc = 1;
+    if (bpc > 16) bpc = 16;
+    if (bpc > batches) bpc = batches;
+    a.batches_per_cta = (int)bpc;
     dim3 grid(ceil_div(batches, a.batches_per_cta), batch);
-    const size_t smem = sizeof(float2) * (M + (size_t)P * fft_buf_len(M));
+    const size_t smem = sizeof(float2) * (2 * (size_t)M + Cfg<M>::TTAB + (size_t)P * fft_buf_len(M));
     MAAVSS_CUDA(cudaFuncSetAttribute(stft_fwd_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    stft_fwd_kernel<M><<<grid, kThreads, smem, st>>>(a);
+    stft_fwd_kernel<M><<<grid, kFwdThreads, smem, st>>>(a);
+    MAAVSS_LAUNCH_CHECK();
+    return MAAVSS_OK;
+}
+
+template <int M, int V>
+int launch_istft_v(const IstftArgs& a, int batch, cudaStream_t st) {
+    constexpr int NT = Cfg<M>::NT;
+    constexpr int P = NT / (M / 16);
+    const int slots = ceil_div(M + a.out_len, a.hop);
+    dim3 grid(ceil_div(slots, a.G), batch);
+    const size_t L = (size_t)(P - 1) * a.hop + 2 * M;
+    const size_t smem = sizeof(float2) * ((size_t)M + Cfg<M>::TTAB + (size_t)P * fft_buf_len(M)) + sizeof(float) * (2 * M + L);
+    MAAVSS_CUDA(cudaFuncSetAttribute(istft_kernel<M, V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    istft_kernel<M, V><<<grid, NT, smem, st>>>(a);
     MAAVSS_LAUNCH_CHECK();
     return MAAVSS_OK;
 }
@@ -182,17 +268,18 @@ int launch_stft(const maavss_stft_plan* p, const StftArgs& a0, int batch, cudaSt
 template <int M>
 int launch_istft(const IstftArgs& a0, int batch, cudaStream_t st) {
     IstftArgs a = a0;
-    constexpr int P = kThreads / (M / 16);
-    int G = 16384 / a.hop;
-    if (G < 1) G = 1;
-    if (G > 64) G = 64;
+    constexpr int P = Cfg<M>::NT / (M / 16);
+    // G hop-slots per CTA: the (n_fft-1)/hop warm-up frames of a strip are recomputed by its neighbour, so
+    // strips are long (<= 6 % recompute) unless the launch would leave SMs idle.
+    const int slots = ceil_div(M + a.out_len, a.hop);
+    const int warm = (2 * M - 1) / a.hop;
+    int G = round_up(max(128, 16 * warm), P);
+    while (G > P && (long long)ceil_div(slots, G) * batch < 148LL * 4) G = round_up(G / 2, P);
     a.G = G;
-    dim3 grid(ceil_div(a.out_len, (long long)G * a.hop), batch);
-    const size_t smem = sizeof(float2) * (M + (size_t)P * fft_buf_len(M)) + sizeof(float) * (size_t)G * a.hop;
-    MAAVSS_CUDA(cudaFuncSetAttribute(istft_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    istft_kernel<M><<<grid, kThreads, smem, st>>>(a);
-    MAAVSS_LAUNCH_CHECK();
-    return MAAVSS_OK;
+    const uintptr_t al = reinterpret_cast<uintptr_t>(a.audio);
+    if (a.hop % 4 == 0 && al % 16 == 0) return launch_istft_v<M, 4>(a, batch, st);
+    if (a.hop % 2 == 0 && al % 8 == 0) return launch_istft_v<M, 2>(a, batch, st);
+    return launch_istft_v<M, 1>(a, batch, st);
 }
 
 bool supported_nfft(int n) { return n >= 64 && n <= 4096 && (n & (n - 1)) == 0; }
@@ -207,20 +294,35 @@ extern "C" int maavss_stft_plan_create(maavss_stft_plan** out, int n_fft, int ho
     p->n_fft = n_fft;
     p->hop = hop;
     const int M = n_fft / 2;
+    const int n_tt = fft_ttab_len(M);
     float2* tw_h = (float2*)malloc(sizeof(float2) * M);
+    float2* tt_h = (float2*)malloc(sizeof(float2) * n_tt);
+    float* ie_h = (float*)malloc(sizeof(float) * hop);
     for (int q = 0; q < M; ++q) {
         const double ang = -2.0 * M_PI * (double)q / (double)n_fft;
         tw_h[q] = make_float2((float)cos(ang), (float)sin(ang));
     }
+    fft_build_ttab(M, tt_h);
     double s = 0.0;
     for (int j = 0; j < n_fft; ++j) s += (double)window_host[j] * (double)window_host[j];
     p->sum_w2 = s;
+    for (int r = 0; r < hop; ++r) {
+        double e = 0.0;
+        for (int j = r; j < n_fft; j += hop) e += (double)window_host[j] * (double)window_host[j];
+        ie_h[r] = (float)(1.0 / e);
+    }
     cudaGetDevice(&p->device);
     cudaError_t e = cudaMalloc(&p->tw, sizeof(float2) * M);
+    if (e == cudaSuccess) e = cudaMalloc(&p->ttab, sizeof(float2) * n_tt);
     if (e == cudaSuccess) e = cudaMalloc(&p->window, sizeof(float) * n_fft);
+    if (e == cudaSuccess) e = cudaMalloc(&p->ienv, sizeof(float) * hop);
     if (e == cudaSuccess) e = cudaMemcpy(p->tw, tw_h, sizeof(float2) * M, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(p->ttab, tt_h, sizeof(float2) * n_tt, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(p->window, window_host, sizeof(float) * n_fft, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(p->ienv, ie_h, sizeof(float) * hop, cudaMemcpyHostToDevice);
     free(tw_h);
+    free(tt_h);
+    free(ie_h);
     if (e != cudaSuccess) {
         maavss_set_error("stft_plan_create: %s", cudaGetErrorString(e));
         maavss_stft_plan_destroy(p);
@@ -234,6 +336,8 @@ extern "C" void maavss_stft_plan_destroy(maavss_stft_plan* p) {
     if (!p) return;
     if (p->tw) cudaFree(p->tw);
     if (p->window) cudaFree(p->window);
+    if (p->ttab) cudaFree(p->ttab);
+    if (p->ienv) cudaFree(p->ienv);
     free(p);
 }
 
@@ -269,6 +373,7 @@ extern "C" int maavss_stft_fwd(const maavss_stft_plan* p, const float* audio, fl
     a.audio = audio;
     a.planes = planes;
     a.tw = p->tw;
+    a.ttab = p->ttab;
     a.window = p->window;
     a.n_samples = n_samples;
     a.hop = p->hop;
@@ -289,7 +394,9 @@ extern "C" int maavss_istft_fwd(const maavss_stft_plan* p, const float* planes, 
     a.planes = planes;
     a.audio = audio;
     a.tw = p->tw;
+    a.ttab = p->ttab;
     a.window = p->window;
+    a.ienv = p->ienv;
     a.hop = p->hop;
     a.T = n_frames;
     a.F_in = trim_stft_end ? p->n_fft / 2 : p->n_fft / 2 + 1;

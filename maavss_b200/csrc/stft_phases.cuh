@@ -4,6 +4,11 @@
 // Reference semantics: AV_Dataset.stft / istft (/root/reference/av_dataset.py:157-201), i.e.
 // torch.stft(center=True, pad_mode="reflect", onesided) / sqrt(sum w^2)   and
 // torch.istft(normalized=True) = irfft(X*sqrt(n)) * w, overlap-add, / sum w^2, centre trim.
+//
+// Scaling is folded into the tables the kernels keep in shared memory:
+//   forward  wsm[j]  = (w[2j], w[2j+1]) * 0.5 * scale            (0.5 = the real-FFT unpack factor)
+//   inverse  wg[s]   = w[s] * 0.5 * scale * (s odd ? -1 : +1)    (the FFT runs on conj(2Z); odd samples come out negated)
+//            ienv[r] = 1 / sum_q w^2[r + q*hop]                   (steady-state overlap-add envelope)
 #pragma once
 #include "fft_core.cuh"
 
@@ -15,40 +20,49 @@ __device__ __forceinline__ int reflect_idx(int p, int n) {
 }
 
 // Load frame t as the packed complex sequence z[j] = x[2j]*w[2j] + i*x[2j+1]*w[2j+1]; thread i keeps
-// elements j = i + m*TPF.
+// elements j = i + m*TPF.  wsm is the (pre-scaled) window as float2 pairs.
 template <int M>
 __device__ __forceinline__ void stft_load_frame(float2 (&v)[16], int i, const float* __restrict__ clip,
-                                                const float* __restrict__ window, int t, int hop,
-                                                int n_samples) {
+                                                const float2* __restrict__ wsm, int t, int hop, int n_samples) {
     constexpr int TPF = M / 16;
     const int base = t * hop - M;  // pad = n_fft/2 = M
     const bool interior = (base >= 0) && (base + 2 * M <= n_samples);
+    if (interior) {
+        const float* p = clip + base + 2 * i;
+        if ((reinterpret_cast<uintptr_t>(p) & 7) == 0) {
 #pragma unroll
-    for (int m = 0; m < 16; ++m) {
-        const int j = i + m * TPF;
-        const float2 w = *reinterpret_cast<const float2*>(window + 2 * j);
-        float x0, x1;
-        if (interior) {
-            x0 = clip[base + 2 * j];
-            x1 = clip[base + 2 * j + 1];
+            for (int m = 0; m < 16; ++m) {
+                const float2 x = *reinterpret_cast<const float2*>(p + 2 * m * TPF);
+                const float2 w = wsm[i + m * TPF];
+                v[m] = make_float2(x.x * w.x, x.y * w.y);
+            }
         } else {
-            x0 = clip[reflect_idx(base + 2 * j, n_samples)];
-            x1 = clip[reflect_idx(base + 2 * j + 1, n_samples)];
+#pragma unroll
+            for (int m = 0; m < 16; ++m) {
+                const float2 w = wsm[i + m * TPF];
+                v[m] = make_float2(p[2 * m * TPF] * w.x, p[2 * m * TPF + 1] * w.y);
+            }
         }
-        v[m] = make_float2(x0 * w.x, x1 * w.y);
+    } else {
+#pragma unroll
+        for (int m = 0; m < 16; ++m) {
+            const int j = i + m * TPF;
+            const float2 w = wsm[j];
+            v[m] = make_float2(clip[reflect_idx(base + 2 * j, n_samples)] * w.x,
+                               clip[reflect_idx(base + 2 * j + 1, n_samples)] * w.y);
+        }
     }
 }
 
-// Z (M-point FFT of the packed sequence, natural order in buf) -> one-sided spectrum X[0..M] of the
-// 2M-point real FFT, scaled, written as one row of the re plane and one row of the im plane
-// (or |X| / atan2 when polar).  Bins >= F_out are dropped (trim_stft_end removes the Nyquist bin).
+// Z (M-point FFT of the packed sequence, natural order in the padded buf) -> one-sided spectrum X[0..M]
+// of the 2M-point real FFT, written as one row of the re plane and one row of the im plane (or |X| /
+// atan2 when polar).  Bins >= F_out are dropped (trim_stft_end removes the Nyquist bin).  tw[k] =
+// exp(-2*pi*i*k/(2M)).
 template <int M>
 __device__ __forceinline__ void stft_post_frame(int i, const float2* __restrict__ buf,
                                                 const float2* __restrict__ tw, float* __restrict__ row0,
-                                                float* __restrict__ row1, int F_out, float scale,
-                                                int polar) {
+                                                float* __restrict__ row1, int F_out, int polar) {
     constexpr int TPF = M / 16;
-    const float hs = 0.5f * scale;
 #pragma unroll
     for (int m = 0; m < 9; ++m) {
         int k = i + m * TPF;            // m < 8: k in [0, M/2); m == 8: the self-paired bin M/2
@@ -61,8 +75,8 @@ __device__ __forceinline__ void stft_post_frame(int i, const float2* __restrict_
         const float2 S = make_float2(A.x + B.x, A.y - B.y);   // A + conj(B)
         const float2 D = make_float2(A.x - B.x, A.y + B.y);   // A - conj(B)
         const float2 WD = cmul(tw[k], D);
-        float2 X0 = make_float2(hs * (S.x + WD.y), hs * (S.y - WD.x));
-        float2 X1 = make_float2(hs * (S.x - WD.y), hs * (-S.y - WD.x));
+        float2 X0 = make_float2(S.x + WD.y, S.y - WD.x);
+        float2 X1 = make_float2(S.x - WD.y, -S.y - WD.x);
         if (polar) {
             X0 = make_float2(sqrtf(X0.x * X0.x + X0.y * X0.y), atan2f(X0.y, X0.x));
             X1 = make_float2(sqrtf(X1.x * X1.x + X1.y * X1.y), atan2f(X1.y, X1.x));
@@ -82,42 +96,149 @@ __device__ __forceinline__ void stft_post_frame(int i, const float2* __restrict_
 // Build conj(Z) for the inverse: Z[k] = 0.5*((X[k] + conj(X[M-k])) + i*exp(+2*pi*i*k/n)*(X[k] - conj(X[M-k])))
 // with the imaginary parts of the DC and Nyquist bins ignored (c2r semantics).  The M-point FFT of
 // conj(Z) is conj(M * z) where z[j] = x[2j] + i*x[2j+1] is the real frame.
-template <int M>
-__device__ __forceinline__ float2 istft_fetch_bin(const float* __restrict__ row0, const float* __restrict__ row1,
-                                                  int k, int F_in, int polar) {
-    if (k >= F_in) return make_float2(0.f, 0.f);   // trimmed Nyquist bin = zero padding (F.pad(stft,(0,1)))
-    float2 x = make_float2(row0[k], row1[k]);
-    if (polar) {
-        float s, c;
-        sincosf(x.y, &s, &c);
-        x = make_float2(x.x * c, x.x * s);
-    }
-    if (k == 0 || k == M) x.y = 0.f;
-    return x;
+__device__ __forceinline__ float2 polar_to_cart(float2 x) {
+    float s, c;
+    sincosf(x.y, &s, &c);
+    return make_float2(x.x * c, x.x * s);
 }
 
+// Thread i loads X[k] and X[M-k] for its k = i + m*TPF (compile-time offsets from two base pointers;
+// each bin is read by the two threads that pair it, the second read hits L1).  Bin M (Nyquist) only
+// exists when F_in = M + 1; trim_stft_end re-pads it with zero (F.pad(stft,(0,1)), av_dataset.py:184).
 template <int M>
 __device__ __forceinline__ void istft_load_frame(float2 (&v)[16], int i, const float* __restrict__ row0,
                                                  const float* __restrict__ row1, int F_in,
                                                  const float2* __restrict__ tw, int polar) {
     constexpr int TPF = M / 16;
+    const float* a0 = row0 + i;
+    const float* a1 = row1 + i;
+    const float* b0 = row0 + (M - i);
+    const float* b1 = row1 + (M - i);
 #pragma unroll
     for (int m = 0; m < 16; ++m) {
-        const int k = i + m * TPF;
-        const float2 A = istft_fetch_bin<M>(row0, row1, k, F_in, polar);
-        const float2 B = istft_fetch_bin<M>(row0, row1, M - k, F_in, polar);
+        float2 A, B;
+        if (m == 0 && i == 0) {
+            A = make_float2(a0[0], polar ? a1[0] : 0.f);
+            B = (F_in > M) ? make_float2(b0[0], polar ? b1[0] : 0.f) : make_float2(0.f, 0.f);
+        } else {
+            A = make_float2(a0[m * TPF], a1[m * TPF]);
+            B = make_float2(b0[-m * TPF], b1[-m * TPF]);
+        }
+        if (polar) {
+            A = polar_to_cart(A);
+            B = polar_to_cart(B);
+            if (m == 0 && i == 0) A.y = B.y = 0.f;      // c2r ignores the imaginary part of DC and Nyquist
+        }
         const float2 S = make_float2(A.x + B.x, A.y - B.y);
         const float2 D = make_float2(A.x - B.x, A.y + B.y);
-        const float2 w = tw[k];                              // exp(-2*pi*i*k/n); need its conjugate
+        const float2 w = tw[i + m * TPF];                    // exp(-2*pi*i*k/n); need its conjugate
         const float2 WD = make_float2(w.x * D.x + w.y * D.y, w.x * D.y - w.y * D.x);   // conj(w)*D
-        // Z = 0.5*(S + i*WD) ; store conj(Z)
-        v[m] = make_float2(0.5f * (S.x - WD.y), -0.5f * (S.y + WD.x));
+        // Z = 0.5*(S + i*WD) ; store conj(2Z) -- the 0.5 is folded into the gather window wg
+        v[m] = make_float2(S.x - WD.y, -(S.y + WD.x));
     }
 }
 
-// Sample s (0 <= s < 2M) of the real frame whose FFT(conj Z) sits in buf (natural order), before
-// the 1/M factor:  x[2j] = Re, x[2j+1] = -Im.
-__device__ __forceinline__ float istft_frame_sample(const float2* __restrict__ buf, int s) {
-    const float2 z = buf[pad_idx(s >> 1)];
-    return (s & 1) ? -z.y : z.x;
+// ---------------------------------------------------------------------------------- overlap-add gather
+// One batch of P consecutive frames [tb, tb+P) sits in shared memory as real sample arrays
+// (frame f at bufs + f*frame_stride, 2M floats, odd samples negated).  acc is a ring of
+// L = (P-1)*hop + N floats holding the partial overlap-add of padded positions [tb*hop, tb*hop + L);
+// position u lives at acc[(u - tb*hop + off) mod L].  After the batch has been added, the first P*hop
+// positions are complete: they are divided by the envelope, stored and cleared; the rest stay in the
+// ring for the next batch (whose window starts P*hop further on).  Each position is touched by
+// exactly one thread per batch, so the overlap-add is deterministic and atomics-free.
+struct IstftGather {
+    int hop, N, M, T;          // geometry (N = n_fft = 2M, T = number of frames)
+    int PH, L;                 // P*hop, ring length
+    int off;                   // ring offset of this batch
+    int nvalid;                // frames of this batch that exist and are needed (others hold garbage)
+    int frame_stride;          // floats between frames in bufs
+    int base_u;                // tb*hop
+    int own_lo, own_hi;        // padded positions this CTA stores
+    float inv_hop;
+};
+
+template <int V>
+struct VecF;
+template <>
+struct VecF<1> {
+    float a[1];
+    __device__ __forceinline__ void load(const float* p) { a[0] = p[0]; }
+    __device__ __forceinline__ void store(float* p) const { p[0] = a[0]; }
+};
+template <>
+struct VecF<2> {
+    float a[2];
+    __device__ __forceinline__ void load(const float* p) {
+        const float2 t = *reinterpret_cast<const float2*>(p);
+        a[0] = t.x; a[1] = t.y;
+    }
+    __device__ __forceinline__ void store(float* p) const { *reinterpret_cast<float2*>(p) = make_float2(a[0], a[1]); }
+};
+template <>
+struct VecF<4> {
+    float a[4];
+    __device__ __forceinline__ void load(const float* p) {
+        const float4 t = *reinterpret_cast<const float4*>(p);
+        a[0] = t.x; a[1] = t.y; a[2] = t.z; a[3] = t.w;
+    }
+    __device__ __forceinline__ void store(float* p) const { *reinterpret_cast<float4*>(p) = make_float4(a[0], a[1], a[2], a[3]); }
+};
+
+// Envelope for one padded position, the slow way (clip edges only).
+__device__ __forceinline__ float istft_env_edge(int u, int hop, int N, int T, const float* __restrict__ wg) {
+    const int tf = (u - N + 1 > 0) ? (u - N + 1 + hop - 1) / hop : 0;
+    const int tl = min(T - 1, u / hop);
+    float env = 0.f;
+    for (int tt = tf; tt <= tl; ++tt) {
+        const float w = wg[u - tt * hop];
+        env = fmaf(w, w, env);
+    }
+    return env;   // wg carries scale: caller divides by scale^2 (see istft_gather_elem)
+}
+
+// Element e of the batch: V consecutive positions starting at u_rel = e*V.
+template <int V>
+__device__ __forceinline__ void istft_gather_elem(int e, const IstftGather& c, float* __restrict__ acc,
+                                                  const float* __restrict__ bufs, const float* __restrict__ wg,
+                                                  const float* __restrict__ ienv, float inv_scale2,
+                                                  float* __restrict__ out_clip) {
+    const int u_rel = e * V;
+    const int q = (int)(((float)u_rel + 0.5f) * c.inv_hop);     // floor(u_rel / hop), exact for these ranges
+    int tr = min(q, c.nvalid - 1);
+    int j = u_rel - tr * c.hop;
+    int pos = u_rel + c.off;
+    if (pos >= c.L) pos -= c.L;
+    VecF<V> val;
+    val.load(acc + pos);
+    const float* fb = bufs + tr * c.frame_stride + j;
+    for (; tr >= 0 && j < c.N; --tr, j += c.hop, fb += c.hop - c.frame_stride) {
+        VecF<V> s, w;
+        s.load(fb);
+        w.load(wg + j);
+#pragma unroll
+        for (int x = 0; x < V; ++x) val.a[x] = fmaf(s.a[x], w.a[x], val.a[x]);
+    }
+    if (u_rel < c.PH) {
+        const int u = c.base_u + u_rel;
+        if (u >= c.own_lo && u < c.own_hi) {
+            VecF<V> o;
+            if (u >= c.N - c.hop && u + V - 1 < c.T * c.hop) {
+                VecF<V> ie;
+                ie.load(ienv + (u_rel - q * c.hop));
+#pragma unroll
+                for (int x = 0; x < V; ++x) o.a[x] = val.a[x] * ie.a[x];
+            } else {
+#pragma unroll
+                for (int x = 0; x < V; ++x)
+                    o.a[x] = val.a[x] / (istft_env_edge(u + x, c.hop, c.N, c.T, wg) * inv_scale2);
+            }
+            o.store(out_clip + (u - c.M));
+        }
+        VecF<V> z;
+#pragma unroll
+        for (int x = 0; x < V; ++x) z.a[x] = 0.f;
+        z.store(acc + pos);
+    } else {
+        val.store(acc + pos);
+    }
 }

@@ -1,36 +1,37 @@
-// Host emulation of the STFT / iSTFT kernels: same phase functions, threads run serially,
-// barriers become loop boundaries.  Built by tests/test_emulation.py with g++.
+// Host emulation of the STFT / iSTFT kernels in maavss_b200/csrc/stft.cu: the same phase functions
+// (stft_phases.cuh / fft_core.cuh) compiled with g++, threads run serially, group / CTA barriers become
+// loop boundaries, the CTA / batch / ring structure is restated 1:1.  Built by tests/test_emulation.py.
 #include "cuda_emu.h"
-#define cudaError_t int
 #include <vector>
-#define CUDA_RUNTIME_H_SHIM
-// fft_core.cuh includes <cuda_runtime.h>; provide an empty stand-in via include path (tests/emu/cuda_runtime.h)
+// fft_core.cuh includes <cuda_runtime.h>; tests/emu/cuda_runtime.h is an empty stand-in on the include path
 #include "../../maavss_b200/csrc/stft_phases.cuh"
 
-template <int M>
-static void fft_block_emu(std::vector<float2>& buf /*M*/, const std::vector<float2>& tw, std::vector<float2>& in_v /*TPF*16*/) {
-    constexpr int TPF = M / 16;
-    constexpr int R1 = (M / 16 >= 16) ? 16 : (M / 16);
-    constexpr int R2 = M / (16 * R1);
+// fft_group of stft.cu with the group barriers turned into loops over the frame's TPF threads.
+template <int M, bool PADFINAL>
+static void fft_group_emu(std::vector<float2>& vin /*TPF*16*/, const float2* ttab, float2* buf) {
+    using S = FftShape<M>;
+    constexpr int TPF = S::TPF;
     float2 v[16];
     std::vector<float2> nxt(fft_buf_len(M));
-    for (int i = 0; i < TPF; ++i) {
-        for (int m = 0; m < 16; ++m) v[m] = in_v[i * 16 + m];
-        fft_pass<M, 16, 1>(v, i, tw.data(), nxt.data());
-    }
-    buf = nxt;
-    for (int i = 0; i < TPF; ++i) {
-        fft_reload<M>(v, i, buf.data());
-        fft_pass<M, R1, 16>(v, i, tw.data(), nxt.data());
-    }
-    buf = nxt;
-    if constexpr (R2 > 1) {
+    auto load = [&](int i) { for (int m = 0; m < 16; ++m) v[m] = vin[i * 16 + m]; };
+    auto reload_all = [&]() {
         for (int i = 0; i < TPF; ++i) {
-            fft_reload<M>(v, i, buf.data());
-            fft_pass<M, R2, 16 * R1>(v, i, tw.data(), nxt.data());
+            fft_reload<M>(v, i, buf);
+            for (int m = 0; m < 16; ++m) vin[i * 16 + m] = v[m];
         }
-        buf = nxt;
+    };
+    for (int i = 0; i < TPF; ++i) { load(i); fft_pass_t<M, 16, 1, 0, true>(v, i, ttab, nxt.data()); }
+    std::memcpy(buf, nxt.data(), sizeof(float2) * nxt.size());
+    reload_all();
+    if constexpr (S::R2 > 1) {
+        for (int i = 0; i < TPF; ++i) { load(i); fft_pass_t<M, S::R1, 16, 0, true>(v, i, ttab, nxt.data()); }
+        std::memcpy(buf, nxt.data(), sizeof(float2) * nxt.size());
+        reload_all();
+        for (int i = 0; i < TPF; ++i) { load(i); fft_pass_t<M, S::R2, 16 * S::R1, S::SLOTS1, PADFINAL>(v, i, ttab, nxt.data()); }
+    } else {
+        for (int i = 0; i < TPF; ++i) { load(i); fft_pass_t<M, S::R1, 16, 0, PADFINAL>(v, i, ttab, nxt.data()); }
     }
+    std::memcpy(buf, nxt.data(), sizeof(float2) * nxt.size());
 }
 
 static std::vector<float2> make_tw(int M) {
@@ -48,75 +49,82 @@ static void stft_emu(const float* clip, int n_samples, int hop, const float* win
     constexpr int TPF = M / 16;
     const int T_out = n_samples / hop;
     auto tw = make_tw(M);
-    std::vector<float2> buf(fft_buf_len(M)), vin(TPF * 16);
+    std::vector<float2> ttab(fft_ttab_len(M)), wsm(M), buf(fft_buf_len(M)), vin(TPF * 16);
+    fft_build_ttab(M, ttab.data());
+    const float hs = 0.5f * scale;
+    for (int q = 0; q < M; ++q) wsm[q] = make_float2(window[2 * q] * hs, window[2 * q + 1] * hs);
     for (int t = 0; t < T_out; ++t) {
         for (int i = 0; i < TPF; ++i) {
             float2 v[16];
-            stft_load_frame<M>(v, i, clip, window, t, hop, n_samples);
+            stft_load_frame<M>(v, i, clip, wsm.data(), t, hop, n_samples);
             for (int m = 0; m < 16; ++m) vin[i * 16 + m] = v[m];
         }
-        fft_block_emu<M>(buf, tw, vin);
+        fft_group_emu<M, true>(vin, ttab.data(), buf.data());
         float* row0 = out + (size_t)t * F_out;
         for (int i = 0; i < TPF; ++i)
-            stft_post_frame<M>(i, buf.data(), tw.data(), row0, row0 + (size_t)T_out * F_out, F_out, scale, polar);
+            stft_post_frame<M>(i, buf.data(), tw.data(), row0, row0 + (size_t)T_out * F_out, F_out, polar);
     }
 }
 
-template <int M>
-static void istft_emu(const float* planes, int T, int F_in, int hop, const float* window, float scale, int polar,
-                      int G, float* audio) {
+template <int M, int V>
+static void istft_emu(const float* planes, int T, int F_in, int hop, const float* window, const float* ienv, float scale,
+                      int polar, int G, float* audio) {
     constexpr int TPF = M / 16;
     constexpr int N = 2 * M;
-    constexpr int P = 256 / TPF;
+    constexpr int NT = (M >= 2048) ? 512 : 256;
+    constexpr int P = NT / TPF;
+    constexpr int FS = 2 * fft_buf_len(M);
     const int out_len = hop * (T - 1);
     auto tw = make_tw(M);
+    std::vector<float2> ttab(fft_ttab_len(M));
+    fft_build_ttab(M, ttab.data());
     const float* in0 = planes;
     const float* in1 = planes + (size_t)T * F_in;
-    const int strips = (out_len + G * hop - 1) / (G * hop);
-    for (int g = 0; g < strips; ++g) {
-        const int s0 = g * G * hop;
-        const int S_out = min(G * hop, out_len - s0);
-        const int u0 = s0 + M;
-        int t_lo = (u0 - N + 1 > 0) ? (u0 - N + 1 + hop - 1) / hop : 0;
-        int t_hi = min(T - 1, (u0 + S_out - 1) / hop);
-        std::vector<float> acc(S_out, 0.f);
-        std::vector<std::vector<float2>> bufs(P, std::vector<float2>(fft_buf_len(M)));
-        for (int tb = t_lo; tb <= t_hi; tb += P) {
-            const int t_last = min(tb + P - 1, t_hi);
-            for (int fi = 0; fi < P && tb + fi <= t_hi; ++fi) {
+    const float sc = 0.5f * scale;
+    const float inv_scale2 = 1.0f / (sc * sc);
+    std::vector<float4> wg4(N / 4);
+    float* wg = reinterpret_cast<float*>(wg4.data());
+    for (int q = 0; q < N; ++q) wg[q] = window[q] * ((q & 1) ? -sc : sc);
+    const int slots = (M + out_len + hop - 1) / hop;
+    for (int bx = 0; bx * G < slots; ++bx) {
+        IstftGather c;
+        c.hop = hop; c.N = N; c.M = M; c.T = T;
+        c.PH = P * hop;
+        c.L = (P - 1) * hop + N;
+        c.frame_stride = FS;
+        c.inv_hop = 1.0f / (float)hop;
+        const int t_a = bx * G, t_b = t_a + G;
+        c.own_lo = max(M, t_a * hop);
+        c.own_hi = min(M + out_len, t_b * hop);
+        const int t_lim = min(t_b, T);
+        const int t_start = max(0, t_a - (N - 1) / hop);
+        std::vector<float4> acc4(c.L / 4 + 1, float4{0, 0, 0, 0}), bufs4((size_t)P * FS / 4 + 1);
+        float* acc = reinterpret_cast<float*>(acc4.data());
+        float* bufs = reinterpret_cast<float*>(bufs4.data());
+        for (size_t q = 0; q < (size_t)P * FS; ++q) bufs[q] = NAN;     // stale shared memory must never be read
+        c.off = 0;
+        for (int tb = t_start; tb * hop < c.own_hi; tb += P) {
+            for (int fi = 0; fi < P; ++fi) {
                 const int t = tb + fi;
+                const int t_group0 = (TPF >= 32) ? t : tb + ((fi * TPF) & ~31) / TPF;
+                if (t_group0 >= t_lim) continue;
                 std::vector<float2> vin(TPF * 16);
                 for (int i = 0; i < TPF; ++i) {
                     float2 v[16];
-                    istft_load_frame<M>(v, i, in0 + (size_t)t * F_in, in1 + (size_t)t * F_in, F_in, tw.data(), polar);
+                    if (t < t_lim) {
+                        istft_load_frame<M>(v, i, in0 + (size_t)t * F_in, in1 + (size_t)t * F_in, F_in, tw.data(), polar);
+                    } else {
+                        for (int m = 0; m < 16; ++m) v[m] = make_float2(0.f, 0.f);
+                    }
                     for (int m = 0; m < 16; ++m) vin[i * 16 + m] = v[m];
                 }
-                fft_block_emu<M>(bufs[fi], tw, vin);
+                fft_group_emu<M, false>(vin, ttab.data(), reinterpret_cast<float2*>(bufs + (size_t)fi * FS));
             }
-            const int lo = max(u0, tb * hop);
-            const int hi = min(u0 + S_out, t_last * hop + N);
-            for (int u = lo; u < hi; ++u) {
-                int tf = (u - N + 1 > 0) ? (u - N + 1 + hop - 1) / hop : 0;
-                tf = max(tf, tb);
-                const int tl = min(t_last, u / hop);
-                float s = 0.f;
-                for (int tt = tf; tt <= tl; ++tt) {
-                    const int j = u - tt * hop;
-                    s += istft_frame_sample(bufs[tt - tb].data(), j) * window[j];
-                }
-                acc[u - u0] += s;
-            }
-        }
-        for (int q = 0; q < S_out; ++q) {
-            const int u = u0 + q;
-            const int tf = (u - N + 1 > 0) ? (u - N + 1 + hop - 1) / hop : 0;
-            const int tl = min(T - 1, u / hop);
-            float env = 0.f;
-            for (int tt = tf; tt <= tl; ++tt) {
-                const float w = window[u - tt * hop];
-                env = fmaf(w, w, env);
-            }
-            audio[s0 + q] = acc[q] * scale / env;
+            c.base_u = tb * hop;
+            c.nvalid = max(0, min(P, t_lim - tb));
+            for (int e = 0; e < c.L / V; ++e) istft_gather_elem<V>(e, c, acc, bufs, wg, ienv, inv_scale2, audio);
+            c.off += c.PH;
+            if (c.off >= c.L) c.off -= c.L;
         }
     }
 }
@@ -143,10 +151,21 @@ extern "C" int emu_stft(const float* clip, int n_samples, int n_fft, int hop, co
     return 0;
 }
 
+// audio must be 16-byte aligned (numpy allocations are).
 extern "C" int emu_istft(const float* planes, int T, int n_fft, int hop, const float* window, int trim, int normalized,
                          int polar, int G, float* audio) {
     const int F_in = trim ? n_fft / 2 : n_fft / 2 + 1;
     const float scale = (float)((normalized ? sqrt((double)n_fft) : 1.0) / (double)(n_fft / 2));
-    DISPATCH(n_fft / 2, istft_emu<MM>(planes, T, F_in, hop, window, scale, polar, G, audio));
+    std::vector<float4> ie4(hop / 4 + 1);
+    float* ienv = reinterpret_cast<float*>(ie4.data());
+    for (int r = 0; r < hop; ++r) {
+        double e = 0;
+        for (int j = r; j < n_fft; j += hop) e += (double)window[j] * window[j];
+        ienv[r] = (float)(1.0 / e);
+    }
+    const int V = (hop % 4 == 0) ? 4 : (hop % 2 == 0) ? 2 : 1;
+    if (V == 4) { DISPATCH(n_fft / 2, (istft_emu<MM, 4>(planes, T, F_in, hop, window, ienv, scale, polar, G, audio))); }
+    else if (V == 2) { DISPATCH(n_fft / 2, (istft_emu<MM, 2>(planes, T, F_in, hop, window, ienv, scale, polar, G, audio))); }
+    else { DISPATCH(n_fft / 2, (istft_emu<MM, 1>(planes, T, F_in, hop, window, ienv, scale, polar, G, audio))); }
     return 0;
 }
