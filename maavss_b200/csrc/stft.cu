@@ -85,7 +85,7 @@ struct StftArgs {
 };
 
 template <int M>
-__global__ void __launch_bounds__(kFwdThreads) stft_fwd_kernel(StftArgs a) {
+__global__ void __launch_bounds__(kFwdThreads, (M <= 256) ? 4 : 3) stft_fwd_kernel(StftArgs a) {
     constexpr int TPF = M / 16;
     constexpr int P = kFwdThreads / TPF;
     extern __shared__ float2 smem[];
@@ -141,7 +141,7 @@ struct IstftArgs {
 // [t_a - (N-1)/hop, min(t_b, T)) in batches of P, inverse-transforms each batch into shared memory
 // and folds it into the overlap-add ring (istft_gather_elem).
 template <int M, int V>
-__global__ void __launch_bounds__(Cfg<M>::NT) istft_kernel(IstftArgs a) {
+__global__ void __launch_bounds__(Cfg<M>::NT, (M <= 256) ? 4 : (M <= 1024 ? 2 : 1)) istft_kernel(IstftArgs a) {
     constexpr int TPF = M / 16;
     constexpr int NT = Cfg<M>::NT;
     constexpr int P = NT / TPF;
@@ -178,22 +178,27 @@ __global__ void __launch_bounds__(Cfg<M>::NT) istft_kernel(IstftArgs a) {
     float* out_clip = a.audio + (size_t)blockIdx.y * a.out_len;
     float2* buf = bufs + fi * fft_buf_len(M);
     c.off = 0;
+    IstftRaw x;
+    istft_fetch_raw<M>(x, i, in0 + (size_t)(t_start + fi) * a.F_in, in1 + (size_t)(t_start + fi) * a.F_in, a.F_in,
+                       t_start + fi < t_lim);
     __syncthreads();
     for (int tb = t_start; tb * hop < c.own_hi; tb += P) {
-        const int t = tb + fi;
         // a warp (or barrier group) whose frames are all beyond t_lim skips the transform altogether
-        const int t_group0 = (TPF >= 32) ? t : tb + (tid & ~31) / TPF;
+        const int t_group0 = (TPF >= 32) ? tb + fi : tb + (tid & ~31) / TPF;
         if (t_group0 < t_lim) {
+            istft_build_z<M>(x, i, tw, a.polar, buf);
+            group_sync<TPF>(fi);
             float2 v[16];
-            if (t < t_lim) {
-                istft_load_frame<M>(v, i, in0 + (size_t)t * a.F_in, in1 + (size_t)t * a.F_in, a.F_in, tw, a.polar);
-            } else {
-#pragma unroll
-                for (int m = 0; m < 16; ++m) v[m] = make_float2(0.f, 0.f);
-            }
+            fft_reload<M>(v, i, buf);
+            group_sync<TPF>(fi);
             fft_group<M, false>(v, i, fi, ttab, buf);
         }
         __syncthreads();
+        {   // raw bins of the next batch travel while this batch is folded into the ring
+            const int tn = tb + P + fi;
+            istft_fetch_raw<M>(x, i, in0 + (size_t)tn * a.F_in, in1 + (size_t)tn * a.F_in, a.F_in,
+                               tn < t_lim && (tb + P) * hop < c.own_hi);
+        }
         c.base_u = tb * hop;
         c.nvalid = max(0, min(P, t_lim - tb));
         for (int e = tid; e < c.L / V; e += NT)

@@ -96,45 +96,93 @@ __device__ __forceinline__ void stft_post_frame(int i, const float2* __restrict_
 // Build conj(Z) for the inverse: Z[k] = 0.5*((X[k] + conj(X[M-k])) + i*exp(+2*pi*i*k/n)*(X[k] - conj(X[M-k])))
 // with the imaginary parts of the DC and Nyquist bins ignored (c2r semantics).  The M-point FFT of
 // conj(Z) is conj(M * z) where z[j] = x[2j] + i*x[2j+1] is the real frame.
+// Inverse input stage.  Thread i owns the bin pairs (k, M-k) for k = i + m*TPF, m < 8 (thread 0 also the
+// self-paired bin M/2), so every bin of the frame is loaded exactly once and the Hermitian unpack shares
+// S, D and W*D between Z[k] and Z[M-k].  The raw values are fetched into registers one batch ahead
+// (istft_fetch_raw, pure loads), turned into conj(2Z) and scattered into the padded exchange buffer
+// (istft_build_z); after a group barrier fft_reload hands every thread its column i + m*TPF.
+// Bin M (Nyquist) only exists when F_in = M + 1; trim_stft_end re-pads it with zero
+// (F.pad(stft,(0,1)), av_dataset.py:184).
+struct IstftRaw {
+    float a[16];   // (re, im) of X[k_m]
+    float b[16];   // (re, im) of X[M - k_m]
+    float s[2];    // thread 0: X[M/2]
+};
+
+template <int M>
+__device__ __forceinline__ void istft_fetch_raw(IstftRaw& x, int i, const float* __restrict__ row0,
+                                                const float* __restrict__ row1, int F_in, bool active) {
+    constexpr int TPF = M / 16;
+    if (!active) {
+#pragma unroll
+        for (int m = 0; m < 16; ++m) x.a[m] = x.b[m] = 0.f;
+        x.s[0] = x.s[1] = 0.f;
+        return;
+    }
+    const float* a0 = row0 + i;
+    const float* a1 = row1 + i;
+    const float* b0 = row0 + (M - i);
+    const float* b1 = row1 + (M - i);
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+        x.a[2 * m] = a0[m * TPF];
+        x.a[2 * m + 1] = a1[m * TPF];
+        if (m == 0 && i == 0) {
+            x.b[0] = (F_in > M) ? b0[0] : 0.f;
+            x.b[1] = (F_in > M) ? b1[0] : 0.f;
+        } else {
+            x.b[2 * m] = b0[-m * TPF];
+            x.b[2 * m + 1] = b1[-m * TPF];
+        }
+    }
+    x.s[0] = x.s[1] = 0.f;
+    if (i == 0) {
+        x.s[0] = row0[M / 2];
+        x.s[1] = row1[M / 2];
+    }
+}
+
 __device__ __forceinline__ float2 polar_to_cart(float2 x) {
     float s, c;
     sincosf(x.y, &s, &c);
     return make_float2(x.x * c, x.x * s);
 }
 
-// Thread i loads X[k] and X[M-k] for its k = i + m*TPF (compile-time offsets from two base pointers;
-// each bin is read by the two threads that pair it, the second read hits L1).  Bin M (Nyquist) only
-// exists when F_in = M + 1; trim_stft_end re-pads it with zero (F.pad(stft,(0,1)), av_dataset.py:184).
+// conj(2 Z[k]) and conj(2 Z[M-k]) from A = X[k], B = X[M-k], w = exp(-2*pi*i*k/n):
+//   S = A + conj(B), D = A - conj(B), WD = conj(w) * D,  2Z[k] = S + i*WD,  2Z[M-k] = conj(S) + i*conj(WD)
+__device__ __forceinline__ void istft_pair(float2 A, float2 B, float2 w, float2& zk, float2& zp) {
+    const float2 S = make_float2(A.x + B.x, A.y - B.y);
+    const float2 D = make_float2(A.x - B.x, A.y + B.y);
+    const float2 WD = make_float2(w.x * D.x + w.y * D.y, w.x * D.y - w.y * D.x);
+    zk = make_float2(S.x - WD.y, -S.y - WD.x);
+    zp = make_float2(S.x + WD.y, S.y - WD.x);
+}
+
 template <int M>
-__device__ __forceinline__ void istft_load_frame(float2 (&v)[16], int i, const float* __restrict__ row0,
-                                                 const float* __restrict__ row1, int F_in,
-                                                 const float2* __restrict__ tw, int polar) {
+__device__ __forceinline__ void istft_build_z(const IstftRaw& x, int i, const float2* __restrict__ tw, int polar,
+                                              float2* __restrict__ buf) {
     constexpr int TPF = M / 16;
-    const float* a0 = row0 + i;
-    const float* a1 = row1 + i;
-    const float* b0 = row0 + (M - i);
-    const float* b1 = row1 + (M - i);
 #pragma unroll
-    for (int m = 0; m < 16; ++m) {
-        float2 A, B;
-        if (m == 0 && i == 0) {
-            A = make_float2(a0[0], polar ? a1[0] : 0.f);
-            B = (F_in > M) ? make_float2(b0[0], polar ? b1[0] : 0.f) : make_float2(0.f, 0.f);
-        } else {
-            A = make_float2(a0[m * TPF], a1[m * TPF]);
-            B = make_float2(b0[-m * TPF], b1[-m * TPF]);
-        }
+    for (int m = 0; m < 8; ++m) {
+        const int k = i + m * TPF;
+        float2 A = make_float2(x.a[2 * m], x.a[2 * m + 1]);
+        float2 B = make_float2(x.b[2 * m], x.b[2 * m + 1]);
         if (polar) {
             A = polar_to_cart(A);
             B = polar_to_cart(B);
-            if (m == 0 && i == 0) A.y = B.y = 0.f;      // c2r ignores the imaginary part of DC and Nyquist
         }
-        const float2 S = make_float2(A.x + B.x, A.y - B.y);
-        const float2 D = make_float2(A.x - B.x, A.y + B.y);
-        const float2 w = tw[i + m * TPF];                    // exp(-2*pi*i*k/n); need its conjugate
-        const float2 WD = make_float2(w.x * D.x + w.y * D.y, w.x * D.y - w.y * D.x);   // conj(w)*D
-        // Z = 0.5*(S + i*WD) ; store conj(2Z) -- the 0.5 is folded into the gather window wg
-        v[m] = make_float2(S.x - WD.y, -(S.y + WD.x));
+        if (m == 0 && i == 0) A.y = B.y = 0.f;      // c2r ignores the imaginary part of DC and Nyquist
+        float2 zk, zp;
+        istft_pair(A, B, tw[k], zk, zp);
+        buf[pad_idx(k)] = zk;
+        if (!(m == 0 && i == 0)) buf[pad_idx(M - k)] = zp;
+    }
+    if (i == 0) {
+        float2 A = make_float2(x.s[0], x.s[1]);
+        if (polar) A = polar_to_cart(A);
+        float2 zk, zp;
+        istft_pair(A, A, tw[M / 2], zk, zp);
+        buf[pad_idx(M / 2)] = zk;
     }
 }
 

@@ -109,13 +109,15 @@ static void istft_emu(const float* planes, int T, int F_in, int hop, const float
                 const int t_group0 = (TPF >= 32) ? t : tb + ((fi * TPF) & ~31) / TPF;
                 if (t_group0 >= t_lim) continue;
                 std::vector<float2> vin(TPF * 16);
+                float2* buf = reinterpret_cast<float2*>(bufs + (size_t)fi * FS);
+                for (int i = 0; i < TPF; ++i) {
+                    IstftRaw x;
+                    istft_fetch_raw<M>(x, i, in0 + (size_t)t * F_in, in1 + (size_t)t * F_in, F_in, t < t_lim);
+                    istft_build_z<M>(x, i, tw.data(), polar, buf);
+                }
                 for (int i = 0; i < TPF; ++i) {
                     float2 v[16];
-                    if (t < t_lim) {
-                        istft_load_frame<M>(v, i, in0 + (size_t)t * F_in, in1 + (size_t)t * F_in, F_in, tw.data(), polar);
-                    } else {
-                        for (int m = 0; m < 16; ++m) v[m] = make_float2(0.f, 0.f);
-                    }
+                    fft_reload<M>(v, i, buf);
                     for (int m = 0; m < 16; ++m) vin[i * 16 + m] = v[m];
                 }
                 fft_group_emu<M, false>(vin, ttab.data(), reinterpret_cast<float2*>(bufs + (size_t)fi * FS));
