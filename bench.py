@@ -144,7 +144,7 @@ def run_reference(args):
             "cpu_baseline": {"value": round(cps, 3), "unit": "clips/s", "cores": threads, "kind": "port",
                              "sample": f"{done} full steps of {B_PER_GPU} clips (same step as the GPU arm), torch CPU, all host threads"},
             "e2e": {"value": round(cps, 3), "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ----------------------------------------------------------------------------------------------------- our arm
@@ -179,7 +179,29 @@ def algorithmic_bytes(name, a):
     return None, ""
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the process's original stdout; everything else (NCCL's version banner, library
+    chatter) was redirected to stderr by quiet_stdout()."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
+def quiet_stdout():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
 def run_ours(args):
+    quiet_stdout()
     import torch
     import torch.distributed as dist
     from maavss_b200 import _lib, av_dataset, avse_model, optim, parallel, train_step
@@ -216,6 +238,8 @@ def run_ours(args):
         return step(x, y, attn)
 
     c0 = L.maavss_launch_count()
+    if args.verbose:
+        print(f"[bench rank {rank}] model built, capturing", file=sys.stderr, flush=True)
     full_step(*resident[0])                                # builds plans, captures the graph (2 warm-up steps inside)
     torch.cuda.synchronize()
     c1 = L.maavss_launch_count()
@@ -244,6 +268,8 @@ def run_ours(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms)
 
+    if args.verbose:
+        print(f"[bench rank {rank}] warm-up done", file=sys.stderr, flush=True)
     clocks = ClockSampler(local)
     clocks.start()
     ms_total = timed(lambda i: full_step(*resident[i % n_sets]))
@@ -285,8 +311,14 @@ def run_ours(args):
             "gpu_launches": launches_per_step * args.steps,
             "final_loss": float(losses[-1][0])}
 
-    if rank == 0:
-        # ---- roofline of the dominant kernel: per-call CUDA-event timing of one eager step (same kernels, same shapes)
+    def note(msg):
+        if args.verbose:
+            print(f"[bench rank {rank}] {msg}", file=sys.stderr, flush=True)
+
+    note("timed regions done")
+    # ---- roofline of the dominant kernel: per-call CUDA-event timing of one eager step (same kernels, same shapes).
+    # Every rank runs it (the step contains the sync-BN and gradient collectives); rank 0 reports.
+    if True:
         pk, pk_kind = peaks()
         prof_step = train_step.FusionTrainStep(model, opt, num_seq=NUM_SEQ, num_frames=NUM_FRAMES, hops_per_frame=HOPS_PER_FRAME,
                                                p_size=64, loss_coeff=LOSS_COEFF, graph=False)
@@ -313,14 +345,23 @@ def run_ours(args):
         line["kernel_breakdown"] = [{"call": f"{n}[{t}]", "share": round(e[0] / tot, 4), "avg_ms": round(e[0] / e[1], 5),
                                      "calls_per_step": e[1] // 3,
                                      "gbs": round(e[2] / (e[0] / e[1] * 1e-3) / 1e9, 1) if e[2] else None} for (n, t), e in top[:12]]
-        if world == 1 and not args.no_cpu:
+        note("profile steps done")
+        if rank == 0 and world == 1 and not args.no_cpu:
             cps, ms_cpu, threads, done = time_cpu(torch, B, 1000, 1, budget_s=args.cpu_seconds)
             line["cpu_baseline"] = {"value": round(cps, 3), "unit": "clips/s", "cores": threads, "kind": "port",
                                     "sample": f"{done} full steps of {B} clips (same step) in {ms_cpu * done / 1e3:.1f} s, oracle on torch CPU"}
-        print(json.dumps(line), flush=True)
+        if rank == 0:
+            emit(line)
     if world > 1:
+        # Tearing the NCCL communicator down while captured graphs still hold its kernels hangs (seen at N=2 on B200):
+        # drop the graphs, drain the device, meet at a barrier and leave without destroy_process_group.
+        step._graph = None
+        torch.cuda.synchronize()
         dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def main():
@@ -332,6 +373,7 @@ def main():
     ap.add_argument("--eager", action="store_true", help="run the step without CUDA-graph capture")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--verbose", action="store_true", help="progress notes on stderr")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3

@@ -85,7 +85,7 @@ struct StftArgs {
 };
 
 template <int M>
-__global__ void __launch_bounds__(kFwdThreads, (M <= 256) ? 4 : 3) stft_fwd_kernel(StftArgs a) {
+__global__ void __launch_bounds__(kFwdThreads, (M <= 256) ? 4 : (M <= 1024 ? 3 : 2)) stft_fwd_kernel(StftArgs a) {
     constexpr int TPF = M / 16;
     constexpr int P = kFwdThreads / TPF;
     extern __shared__ float2 smem[];
@@ -133,14 +133,16 @@ struct IstftArgs {
     const float2* ttab;
     const float* window;
     const float* ienv;
-    int hop, T, F_in, G, polar, out_len;
+    int hop, T, F_in, G, polar, out_len, log2C;
     float scale;
 };
 
 // One CTA owns G hop-slots of one clip: padded positions [t_a*hop, t_b*hop).  It walks the frames
 // [t_a - (N-1)/hop, min(t_b, T)) in batches of P, inverse-transforms each batch into shared memory
 // and folds it into the overlap-add ring (istft_gather_elem).
-template <int M, int V>
+// V = vector width of the generic gather (any hop); R > 0 selects the column-owning gather (hop a power of two,
+// R = n_fft / hop, V = 4).
+template <int M, int V, int R>
 __global__ void __launch_bounds__(Cfg<M>::NT, (M <= 256) ? 4 : (M <= 1024 ? 2 : 1)) istft_kernel(IstftArgs a) {
     constexpr int TPF = M / 16;
     constexpr int NT = Cfg<M>::NT;
@@ -178,6 +180,19 @@ __global__ void __launch_bounds__(Cfg<M>::NT, (M <= 256) ? 4 : (M <= 1024 ? 2 : 
     float* out_clip = a.audio + (size_t)blockIdx.y * a.out_len;
     float2* buf = bufs + fi * fft_buf_len(M);
     c.off = 0;
+    constexpr int RR = (R > 0) ? R : 1;
+    constexpr bool WREG = (R > 0 && R <= 4);
+    float4 wr[RR];
+    float4 ie = make_float4(0.f, 0.f, 0.f, 0.f);
+    if constexpr (R > 0) {
+        const int col4 = (tid & ((hop >> 2) - 1)) * 4;
+        ie = *reinterpret_cast<const float4*>(a.ienv + col4);
+#pragma unroll
+        for (int s = 0; s < RR; ++s) {
+            const float4 w = *reinterpret_cast<const float4*>(a.window + col4 + s * hop);
+            wr[s] = make_float4(w.x * sc, -w.y * sc, w.z * sc, -w.w * sc);   // == wg[col4 + s*hop ..]
+        }
+    }
     IstftRaw x;
     istft_fetch_raw<M>(x, i, in0 + (size_t)(t_start + fi) * a.F_in, in1 + (size_t)(t_start + fi) * a.F_in, a.F_in,
                        t_start + fi < t_lim);
@@ -201,8 +216,13 @@ __global__ void __launch_bounds__(Cfg<M>::NT, (M <= 256) ? 4 : (M <= 1024 ? 2 : 
         }
         c.base_u = tb * hop;
         c.nvalid = max(0, min(P, t_lim - tb));
-        for (int e = tid; e < c.L / V; e += NT)
-            istft_gather_elem<V>(e, c, acc, reinterpret_cast<const float*>(bufs), wg, a.ienv, inv_scale2, out_clip);
+        if constexpr (R > 0) {
+            istft_gather_cols<RR, WREG>(tid, NT, a.log2C, P, c, acc, reinterpret_cast<const float*>(bufs), wg, wr, ie,
+                                        inv_scale2, out_clip);
+        } else {
+            for (int e = tid; e < c.L / V; e += NT)
+                istft_gather_elem<V>(e, c, acc, reinterpret_cast<const float*>(bufs), wg, a.ienv, inv_scale2, out_clip);
+        }
         c.off += c.PH;
         if (c.off >= c.L) c.off -= c.L;
         __syncthreads();
@@ -256,7 +276,7 @@ int launch_stft(const maavss_stft_plan* p, const StftArgs& a0, int batch, cudaSt
     return MAAVSS_OK;
 }
 
-template <int M, int V>
+template <int M, int V, int R>
 int launch_istft_v(const IstftArgs& a, int batch, cudaStream_t st) {
     constexpr int NT = Cfg<M>::NT;
     constexpr int P = NT / (M / 16);
@@ -264,8 +284,8 @@ int launch_istft_v(const IstftArgs& a, int batch, cudaStream_t st) {
     dim3 grid(ceil_div(slots, a.G), batch);
     const size_t L = (size_t)(P - 1) * a.hop + 2 * M;
     const size_t smem = sizeof(float2) * ((size_t)M + Cfg<M>::TTAB + (size_t)P * fft_buf_len(M)) + sizeof(float) * (2 * M + L);
-    MAAVSS_CUDA(cudaFuncSetAttribute(istft_kernel<M, V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    istft_kernel<M, V><<<grid, NT, smem, st>>>(a);
+    MAAVSS_CUDA(cudaFuncSetAttribute(istft_kernel<M, V, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    istft_kernel<M, V, R><<<grid, NT, smem, st>>>(a);
     MAAVSS_LAUNCH_CHECK();
     return MAAVSS_OK;
 }
@@ -282,9 +302,24 @@ int launch_istft(const IstftArgs& a0, int batch, cudaStream_t st) {
     while (G > P && (long long)ceil_div(slots, G) * batch < 148LL * 4) G = round_up(G / 2, P);
     a.G = G;
     const uintptr_t al = reinterpret_cast<uintptr_t>(a.audio);
-    if (a.hop % 4 == 0 && al % 16 == 0) return launch_istft_v<M, 4>(a, batch, st);
-    if (a.hop % 2 == 0 && al % 8 == 0) return launch_istft_v<M, 2>(a, batch, st);
-    return launch_istft_v<M, 1>(a, batch, st);
+    // the column-owning gather keeps R window vectors in registers: it pays for M >= 512 (measured), where the
+    // kernel is not held to 64 registers, and for R <= 4
+    if constexpr (M >= 512) {
+        const bool pow2 = (a.hop & (a.hop - 1)) == 0;
+        if (pow2 && a.hop >= 4 && a.hop / 4 <= Cfg<M>::NT && al % 16 == 0 && (2 * M) % a.hop == 0) {
+            a.log2C = 0;
+            while ((4 << a.log2C) < a.hop) ++a.log2C;
+            switch (2 * M / a.hop) {
+                case 1: return launch_istft_v<M, 4, 1>(a, batch, st);
+                case 2: return launch_istft_v<M, 4, 2>(a, batch, st);
+                case 4: return launch_istft_v<M, 4, 4>(a, batch, st);
+                default: break;
+            }
+        }
+    }
+    if (a.hop % 4 == 0 && al % 16 == 0) return launch_istft_v<M, 4, 0>(a, batch, st);
+    if (a.hop % 2 == 0 && al % 8 == 0) return launch_istft_v<M, 2, 0>(a, batch, st);
+    return launch_istft_v<M, 1, 0>(a, batch, st);
 }
 
 bool supported_nfft(int n) { return n >= 64 && n <= 4096 && (n & (n - 1)) == 0; }
@@ -409,6 +444,7 @@ extern "C" int maavss_istft_fwd(const maavss_stft_plan* p, const float* planes, 
     a.out_len = p->hop * (n_frames - 1);
     a.scale = (float)((normalized ? sqrt((double)p->n_fft) : 1.0) / (double)(p->n_fft / 2));
     a.G = 1;
+    a.log2C = 0;
     cudaStream_t st = (cudaStream_t)stream;
     int rc = MAAVSS_OK;
     DISPATCH_M(p->n_fft / 2, rc = launch_istft<MM>(a, batch, st));

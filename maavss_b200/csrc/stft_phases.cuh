@@ -290,3 +290,57 @@ __device__ __forceinline__ void istft_gather_elem(int e, const IstftGather& c, f
         val.store(acc + pos);
     }
 }
+
+// Column-owning variant for power-of-two hops that divide n_fft (R = n_fft / hop frames overlap).  A thread
+// keeps one float4 column (4*col .. 4*col+3 within the hop) for the whole kernel, so its R window vectors
+// and its envelope vector stay in registers (wr, ie) and the frame loop is fully unrolled: one LDS.128
+// per (position, frame) instead of two plus loop control.  rows = P - 1 + R hop-rows per batch.
+template <int R, bool WREG>
+__device__ __forceinline__ void istft_gather_cols(int tid, int nthreads, int log2C, int P, const IstftGather& c,
+                                                  float* __restrict__ acc, const float* __restrict__ bufs,
+                                                  const float* __restrict__ wg, const float4 (&wr)[R], float4 ie,
+                                                  float inv_scale2, float* __restrict__ out_clip) {
+    const int C = 1 << log2C;
+    const int col4 = (tid & (C - 1)) * 4;
+    const int rows_per_pass = nthreads >> log2C;
+    const int nrows = P - 1 + R;
+    for (int q = tid >> log2C; q < nrows; q += rows_per_pass) {
+        const int u_rel = q * c.hop + col4;
+        int pos = u_rel + c.off;
+        if (pos >= c.L) pos -= c.L;
+        float4 val = *reinterpret_cast<const float4*>(acc + pos);
+        const float* fb = bufs + q * c.frame_stride + col4;
+#pragma unroll
+        for (int s = 0; s < R; ++s) {
+            const int tr = q - s;
+            if (tr >= 0 && tr < c.nvalid) {
+                const float4 f = *reinterpret_cast<const float4*>(fb + s * (c.hop - c.frame_stride));
+                float4 w;
+                if constexpr (WREG) w = wr[s];
+                else w = *reinterpret_cast<const float4*>(wg + col4 + s * c.hop);
+                val.x = fmaf(f.x, w.x, val.x);
+                val.y = fmaf(f.y, w.y, val.y);
+                val.z = fmaf(f.z, w.z, val.z);
+                val.w = fmaf(f.w, w.w, val.w);
+            }
+        }
+        if (q < P) {
+            const int u = c.base_u + u_rel;
+            if (u >= c.own_lo && u < c.own_hi) {
+                float4 o;
+                if (u >= c.N - c.hop && u + 3 < c.T * c.hop) {
+                    o = make_float4(val.x * ie.x, val.y * ie.y, val.z * ie.z, val.w * ie.w);
+                } else {
+                    o.x = val.x / (istft_env_edge(u, c.hop, c.N, c.T, wg) * inv_scale2);
+                    o.y = val.y / (istft_env_edge(u + 1, c.hop, c.N, c.T, wg) * inv_scale2);
+                    o.z = val.z / (istft_env_edge(u + 2, c.hop, c.N, c.T, wg) * inv_scale2);
+                    o.w = val.w / (istft_env_edge(u + 3, c.hop, c.N, c.T, wg) * inv_scale2);
+                }
+                *reinterpret_cast<float4*>(out_clip + (u - c.M)) = o;
+            }
+            *reinterpret_cast<float4*>(acc + pos) = make_float4(0.f, 0.f, 0.f, 0.f);
+        } else {
+            *reinterpret_cast<float4*>(acc + pos) = val;
+        }
+    }
+}

@@ -66,7 +66,7 @@ static void stft_emu(const float* clip, int n_samples, int hop, const float* win
     }
 }
 
-template <int M, int V>
+template <int M, int V, int R>
 static void istft_emu(const float* planes, int T, int F_in, int hop, const float* window, const float* ienv, float scale,
                       int polar, int G, float* audio) {
     constexpr int TPF = M / 16;
@@ -124,7 +124,22 @@ static void istft_emu(const float* planes, int T, int F_in, int hop, const float
             }
             c.base_u = tb * hop;
             c.nvalid = max(0, min(P, t_lim - tb));
-            for (int e = 0; e < c.L / V; ++e) istft_gather_elem<V>(e, c, acc, bufs, wg, ienv, inv_scale2, audio);
+            if constexpr (R > 0) {
+                int log2C = 0;
+                while ((4 << log2C) < hop) ++log2C;
+                for (int tid = 0; tid < NT; ++tid) {
+                    const int col4 = (tid & ((hop >> 2) - 1)) * 4;
+                    float4 wr[R];
+                    for (int s2 = 0; s2 < R; ++s2) {
+                        const float* w = window + col4 + s2 * hop;
+                        wr[s2] = make_float4(w[0] * sc, -w[1] * sc, w[2] * sc, -w[3] * sc);
+                    }
+                    const float4 ie = *reinterpret_cast<const float4*>(ienv + col4);
+                    istft_gather_cols<R, (R <= 4)>(tid, NT, log2C, P, c, acc, bufs, wg, wr, ie, inv_scale2, audio);
+                }
+            } else {
+                for (int e = 0; e < c.L / V; ++e) istft_gather_elem<V>(e, c, acc, bufs, wg, ienv, inv_scale2, audio);
+            }
             c.off += c.PH;
             if (c.off >= c.L) c.off -= c.L;
         }
@@ -166,8 +181,15 @@ extern "C" int emu_istft(const float* planes, int T, int n_fft, int hop, const f
         ienv[r] = (float)(1.0 / e);
     }
     const int V = (hop % 4 == 0) ? 4 : (hop % 2 == 0) ? 2 : 1;
-    if (V == 4) { DISPATCH(n_fft / 2, (istft_emu<MM, 4>(planes, T, F_in, hop, window, ienv, scale, polar, G, audio))); }
-    else if (V == 2) { DISPATCH(n_fft / 2, (istft_emu<MM, 2>(planes, T, F_in, hop, window, ienv, scale, polar, G, audio))); }
-    else { DISPATCH(n_fft / 2, (istft_emu<MM, 1>(planes, T, F_in, hop, window, ienv, scale, polar, G, audio))); }
+    const bool pow2 = (hop & (hop - 1)) == 0;
+    const int NT = (n_fft / 2 >= 2048) ? 512 : 256;
+    int R = (pow2 && hop >= 4 && hop / 4 <= NT && n_fft % hop == 0 && n_fft >= 1024) ? n_fft / hop : 0;
+    if (R > 4) R = 0;   // same dispatch rule as launch_istft in stft.cu
+    if (R == 1) { DISPATCH(n_fft / 2, (istft_emu<MM, 4, 1>(planes, T, F_in, hop, window, ienv, scale, polar, G, audio))); }
+    else if (R == 2) { DISPATCH(n_fft / 2, (istft_emu<MM, 4, 2>(planes, T, F_in, hop, window, ienv, scale, polar, G, audio))); }
+    else if (R == 4) { DISPATCH(n_fft / 2, (istft_emu<MM, 4, 4>(planes, T, F_in, hop, window, ienv, scale, polar, G, audio))); }
+    else if (V == 4) { DISPATCH(n_fft / 2, (istft_emu<MM, 4, 0>(planes, T, F_in, hop, window, ienv, scale, polar, G, audio))); }
+    else if (V == 2) { DISPATCH(n_fft / 2, (istft_emu<MM, 2, 0>(planes, T, F_in, hop, window, ienv, scale, polar, G, audio))); }
+    else { DISPATCH(n_fft / 2, (istft_emu<MM, 1, 0>(planes, T, F_in, hop, window, ienv, scale, polar, G, audio))); }
     return 0;
 }

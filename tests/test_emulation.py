@@ -31,7 +31,8 @@ def fptr(a):
 
 @pytest.mark.parametrize("n_fft,hop,n", [(64, 16, 500), (128, 32, 700), (256, 66, 6336), (512, 128, 3000),
                                          (1024, 256, 5000), (2048, 512, 9000), (4096, 1024, 12000), (256, 100, 3001),
-                                         (256, 77, 3000), (128, 128, 1000), (512, 300, 4000), (4096, 512, 30000)])
+                                         (256, 77, 3000), (128, 128, 1000), (512, 300, 4000), (4096, 512, 30000),
+                                         (4096, 2048, 30000), (2048, 1024, 9000), (1024, 64, 5000), (512, 8, 2000), (1024, 1024, 9000)])
 @pytest.mark.parametrize("trim", [1, 0])
 def test_stft_istft_emulated(emu, n_fft, hop, n, trim):
     g = torch.Generator().manual_seed(n_fft + hop)
