@@ -85,7 +85,7 @@ struct StftArgs {
 };
 
 template <int M>
-__global__ void __launch_bounds__(kFwdThreads, (M <= 256) ? 4 : (M <= 1024 ? 3 : 2)) stft_fwd_kernel(StftArgs a) {
+__global__ void __launch_bounds__(kFwdThreads, (M <= 256) ? 4 : 3) stft_fwd_kernel(StftArgs a) {
     constexpr int TPF = M / 16;
     constexpr int P = kFwdThreads / TPF;
     extern __shared__ float2 smem[];

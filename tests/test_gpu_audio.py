@@ -84,9 +84,11 @@ def test_stft_index_exact_impulses(ops):
         assert torch.equal(out.abs().amax(dim=(0, 2)) == 0, ref.abs().amax(dim=(0, 2)) == 0)
 
 
-def test_stft_large_batch_roundtrip(ops):
-    """Full-size property test (config 5 shape): istft(stft(x)) == gain * x away from the edges."""
-    n_fft, hop, B, n = 1024, 256, 64, 160000
+@pytest.mark.parametrize("n_fft,hop,B", [(1024, 256, 64), (4096, 512, 128), (4096, 2048, 96), (512, 64, 256), (256, 66, 300)])
+def test_stft_large_batch_roundtrip(ops, n_fft, hop, B):
+    """Full-size property test (config 5 shape: 10 s clips, batches large enough that a CTA walks several frame
+    batches): istft(stft(x)) == gain * x away from the edges."""
+    n = 160000
     audio = torch.randn(B, n, generator=torch.Generator().manual_seed(1)).cuda()
     w = oa.hamming_window(n_fft)
     planes = ops.stft_planes(audio, w, n_fft, hop, False)
