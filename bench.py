@@ -345,6 +345,12 @@ def run_ours(args):
         line["kernel_breakdown"] = [{"call": f"{n}[{t}]", "share": round(e[0] / tot, 4), "avg_ms": round(e[0] / e[1], 5),
                                      "calls_per_step": e[1] // 3,
                                      "gbs": round(e[2] / (e[0] / e[1] * 1e-3) / 1e9, 1) if e[2] else None} for (n, t), e in top[:12]]
+        if args.breakdown and rank == 0:
+            with open(args.breakdown, "w") as f:
+                for (n, t), e in top:
+                    f.write(f"{100 * e[0] / tot:6.2f}%  calls/step={e[1] // 3:3d}  avg_ms={e[0] / e[1]:8.5f}  "
+                            f"GB/s={(e[2] / (e[0] / e[1] * 1e-3) / 1e9) if e[2] else float('nan'):8.1f}  {n}[{t}]\n")
+                f.write(f"# eager step total {tot / 3:.3f} ms (sum of per-call CUDA-event times)\n")
         note("profile steps done")
         if rank == 0 and world == 1 and not args.no_cpu:
             cps, ms_cpu, threads, done = time_cpu(torch, B, 1000, 1, budget_s=args.cpu_seconds)
@@ -374,6 +380,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--verbose", action="store_true", help="progress notes on stderr")
+    ap.add_argument("--breakdown", default=None, help="write the full per-call breakdown of the eager profiling steps to this file")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3

@@ -286,6 +286,72 @@ __global__ void __launch_bounds__(256, 2) lin_wgrad_kernel(const float* __restri
     }
 }
 
+// Same product for 16 < M <= 64 rows (the four accumulation windows of a 16-clip batch stacked along M,
+// train_step.FusionTrainStep): the activations no longer fit in registers for all m, so a thread keeps 8 rows x
+// one float4 of dw as accumulators and walks m in chunks of 16 (x chunk in registers, L1/L2 resident; dz tile in
+// shared memory).  dw is still read (when accumulating) and written exactly once.
+constexpr int WG_MMAX = 64;
+__global__ void __launch_bounds__(256, 2) lin_wgrad_wide_kernel(const float* __restrict__ dz, const float* __restrict__ x,
+                                                                float* __restrict__ dw, float* __restrict__ dbias, int M, int N,
+                                                                int K, int accumulate, int kx) {
+    __shared__ __align__(16) float dzs[WG_ROWS * WG_MMAX];   // [row][m]
+    const int tx = threadIdx.x % kx, ty = threadIdx.x / kx, ny = 256 / kx;
+    const int k4 = (blockIdx.x * kx + tx) * 4;
+    const bool kok = k4 < K;
+    const int n0 = blockIdx.y * WG_ROWS;
+    for (int e = threadIdx.x; e < WG_ROWS * WG_MMAX; e += 256) {
+        const int j = e % WG_ROWS, m = e / WG_ROWS;
+        dzs[j * WG_MMAX + m] = (m < M && n0 + j < N) ? dz[(size_t)m * N + n0 + j] : 0.f;
+    }
+    __syncthreads();
+    if (dbias && blockIdx.x == 0 && threadIdx.x < WG_ROWS && n0 + threadIdx.x < N) {
+        float s = 0.f;
+        for (int m = 0; m < M; ++m) s += dzs[threadIdx.x * WG_MMAX + m];
+        dbias[n0 + threadIdx.x] = accumulate ? dbias[n0 + threadIdx.x] + s : s;
+    }
+    if (!kok) return;
+    const int rows = min(WG_ROWS, N - n0);
+    const int mchunks = (M + MT - 1) / MT;
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int j0 = ty; j0 < rows; j0 += 8 * ny) {
+        float4 a[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int j = j0 + u * ny;
+            a[u] = (accumulate && j < rows) ? ldg_stream(dw + (size_t)(n0 + j) * K + k4) : zero4;
+        }
+        for (int mc = 0; mc < mchunks; ++mc) {
+            float4 xr[MT];
+#pragma unroll
+            for (int mm = 0; mm < MT; ++mm) {
+                const int m = mc * MT + mm;
+                xr[mm] = (m < M) ? *reinterpret_cast<const float4*>(x + (size_t)m * K + k4) : zero4;
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int j = min(j0 + u * ny, rows - 1);      // rows past the end recompute the last one and are not stored
+                const float4* dzr = reinterpret_cast<const float4*>(&dzs[j * WG_MMAX + mc * MT]);
+#pragma unroll
+                for (int mq = 0; mq < 4; ++mq) {
+                    const float4 d = dzr[mq];
+                    const float dm[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+                    for (int mm = 0; mm < 4; ++mm) {
+                        const float4 xv = xr[mq * 4 + mm];
+                        a[u].x = fmaf(dm[mm], xv.x, a[u].x); a[u].y = fmaf(dm[mm], xv.y, a[u].y);
+                        a[u].z = fmaf(dm[mm], xv.z, a[u].z); a[u].w = fmaf(dm[mm], xv.w, a[u].w);
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int j = j0 + u * ny;
+            if (j < rows) *reinterpret_cast<float4*>(dw + (size_t)(n0 + j) * K + k4) = a[u];
+        }
+    }
+}
+
 }  // namespace skinny
 
 // ------------------------------------------------------------------------------------------------ host launchers
@@ -336,11 +402,12 @@ int maavss_skinny_dgrad(const float* dz, const float* w, float* dx, int M, int N
 
 int maavss_skinny_wgrad(const float* dz, const float* x, float* dw, float* dbias, int M, int N, int K, int accumulate,
                         cudaStream_t st) {
-    if (M > skinny::MT || K % 4 != 0) return 0;
+    if (M > skinny::WG_MMAX || K % 4 != 0) return 0;
     if (((uintptr_t)x | (uintptr_t)dw) & 15) return 0;
     const int kx = pow2_at_most(K / 4 > 0 ? K / 4 : 1, 256);
     dim3 grid(ceil_div(K / 4, kx), ceil_div(N, skinny::WG_ROWS));
-    skinny::lin_wgrad_kernel<<<grid, 256, 0, st>>>(dz, x, dw, dbias, M, N, K, accumulate, kx);
+    if (M <= skinny::MT) skinny::lin_wgrad_kernel<<<grid, 256, 0, st>>>(dz, x, dw, dbias, M, N, K, accumulate, kx);
+    else skinny::lin_wgrad_wide_kernel<<<grid, 256, 0, st>>>(dz, x, dw, dbias, M, N, K, accumulate, kx);
     MAAVSS_LAUNCH_CHECK();
     return 1;
 }

@@ -142,7 +142,8 @@ def test_batchnorm_act(shape, act):
 
 
 @pytest.mark.parametrize("M,K,N", [(16, 4096, 2048), (16, 512, 16384), (1, 2048, 512), (128, 512, 1024), (37, 100, 77),
-                                   (5, 132, 45), (16, 2048, 512), (32, 8192, 100), (16, 512, 32768), (48, 260, 70)])
+                                   (5, 132, 45), (16, 2048, 512), (32, 8192, 100), (16, 512, 32768), (48, 260, 70),
+                                   (64, 512, 16384), (64, 4096, 2048), (63, 2048, 130)])
 @pytest.mark.parametrize("act", ["leaky", "tanh", "sigmoid", "none"])
 def test_linear(M, K, N, act):
     from maavss_b200 import layers as L
