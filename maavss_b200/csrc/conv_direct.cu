@@ -110,9 +110,10 @@ int maavss_conv_wgrad_direct(const maavss_conv_desc* d, const float* x, const fl
     const long long P = (long long)d->N * g.O;
     const int J = d->Cin * g.KV;
     const int gy = ceil_div(J, direct::WG_J), gz = ceil_div(d->Cout, direct::WG_CO);
-    // cost model: every (column block, channel block) pair walks all positions; beyond ~16 M position-passes the
-    // tiled implicit GEMM (operand reuse through shared memory) wins
-    if (P >= (1LL << 31) || (long long)gy * gz * P > (16LL << 20) || gy > 65535 || gz > 65535) return 0;
+    // envelope (measured on B200, bench.py --breakdown): every (column block, channel block) pair walks all positions
+    // and re-reads dy / x, so the kernel wins for the thin layers (<= 24 block pairs: C1->2 ... C8->16 with 1x9 taps,
+    // C2->8 with 5x5) by 4-30x and loses 20-30 % to the tiled implicit GEMM beyond that
+    if (P >= (1LL << 31) || (long long)gy * gz > 24 || (long long)gy * gz * P > (16LL << 20)) return 0;
     const int sms = maavss_num_sms();
     long long want_x = (4LL * sms + (long long)gy * gz - 1) / ((long long)gy * gz);      // ~4 CTAs per SM overall
     if (want_x < 1) want_x = 1;
@@ -128,6 +129,107 @@ int maavss_conv_wgrad_direct(const maavss_conv_desc* d, const float* x, const fl
     }
     dim3 grid(ceil_div(P, ppc), gy, gz);
     direct::wgrad_kernel<<<grid, direct::WG_T, 0, st>>>(g, x, dy, dw, (int)P, (int)ppc, J);
+    MAAVSS_LAUNCH_CHECK();
+    return 1;
+}
+
+// ---------------------------------------------------------------------------------------------- DGRAD
+namespace direct {
+
+constexpr int DG_T = 256, DG_WS = 8192;     // threads (= input positions) per CTA, floats of staged weights
+
+__device__ __forceinline__ int div_small(int t, int S) { return S == 1 ? t : (S == 2 ? t >> 1 : t / S); }
+
+// dx[n, ci, q] = sum_{co} sum_{o : q + pad - o*stride is a tap} dy[n, co, o] * w[co, ci, tap]  (+ bias[ci]).
+// A thread owns one input position q and CI_T input channels.  The output positions that reach q form a small
+// box [od_min..od_max] x [oh_min..oh_max] x [ow_min..ow_max] computed once per thread, so the inner loops run over
+// contributing taps only (1/(SD*SH*SW) of the kernel volume for a strided layer) with no divisibility tests.
+// Weights are staged per group of output channels as ws[co][tap][CI_T] so a tap is one LDS.128 per 4 channels.
+template <int CI_T>
+__global__ void __launch_bounds__(DG_T) dgrad_kernel(Geo g, const float* __restrict__ dy, const float* __restrict__ w,
+                                                     const float* __restrict__ bias, float* __restrict__ dx, int Q,
+                                                     int co_chunk) {
+    __shared__ __align__(16) float ws[DG_WS];
+    const maavss_conv_desc& d = g.d;
+    const int ci0 = blockIdx.y * CI_T;
+    const int q = blockIdx.x * DG_T + threadIdx.x;
+    const bool valid = q < Q;
+    const int qq = valid ? q : 0;
+    const int n = qq / g.I;
+    const int pos = qq - n * g.I;
+    const int id = pos / g.HW;
+    const int r = pos - id * g.HW;
+    const int ih = r / d.W, iw = r - ih * d.W;
+    const int td = id + d.PD, th = ih + d.PH, tw = iw + d.PW;
+    const int od_lo = (td - d.KD + 1 <= 0) ? 0 : div_small(td - d.KD + d.SD, d.SD), od_hi = min(d.OD - 1, div_small(td, d.SD));
+    const int oh_lo = (th - d.KH + 1 <= 0) ? 0 : div_small(th - d.KH + d.SH, d.SH), oh_hi = min(d.OH - 1, div_small(th, d.SH));
+    const int ow_lo = (tw - d.KW + 1 <= 0) ? 0 : div_small(tw - d.KW + d.SW, d.SW), ow_hi = min(d.OW - 1, div_small(tw, d.SW));
+    float acc[CI_T];
+#pragma unroll
+    for (int c = 0; c < CI_T; ++c) acc[c] = 0.f;
+    for (int co0 = 0; co0 < d.Cout; co0 += co_chunk) {
+        const int cc = min(co_chunk, d.Cout - co0);
+        __syncthreads();
+        for (int e = threadIdx.x; e < cc * g.KV * CI_T; e += DG_T) {
+            const int c = e % CI_T, rr = e / CI_T;
+            const int tap = rr % g.KV, col = rr / g.KV;
+            const int ci = ci0 + c;
+            ws[e] = (ci < d.Cin) ? __ldg(w + ((size_t)(co0 + col) * d.Cin + ci) * g.KV + tap) : 0.f;
+        }
+        __syncthreads();
+        if (!valid) continue;
+        for (int col = 0; col < cc; ++col) {
+            const float* dyp = dy + ((size_t)n * d.Cout + co0 + col) * g.O;
+            const float* wp = ws + col * g.KV * CI_T;
+            for (int od = od_lo; od <= od_hi; ++od) {
+                const int kd = td - od * d.SD;
+                for (int oh = oh_lo; oh <= oh_hi; ++oh) {
+                    const int kh = th - oh * d.SH;
+                    const float* dyr = dyp + od * g.OHW + oh * d.OW;
+                    const float* wr = wp + ((kd * d.KH + kh) * d.KW + tw) * CI_T;      // + (-ow*SW)*CI_T below
+                    for (int ow = ow_lo; ow <= ow_hi; ++ow) {
+                        const float dyv = __ldg(dyr + ow);
+                        const float4* w4 = reinterpret_cast<const float4*>(wr - ow * d.SW * CI_T);
+#pragma unroll
+                        for (int c4 = 0; c4 < CI_T / 4; ++c4) {
+                            const float4 wv = w4[c4];
+                            acc[4 * c4 + 0] = fmaf(dyv, wv.x, acc[4 * c4 + 0]);
+                            acc[4 * c4 + 1] = fmaf(dyv, wv.y, acc[4 * c4 + 1]);
+                            acc[4 * c4 + 2] = fmaf(dyv, wv.z, acc[4 * c4 + 2]);
+                            acc[4 * c4 + 3] = fmaf(dyv, wv.w, acc[4 * c4 + 3]);
+                        }
+                    }
+                }
+            }
+        }
+    }
+    if (!valid) return;
+#pragma unroll
+    for (int c = 0; c < CI_T; ++c) {
+        const int ci = ci0 + c;
+        if (ci < d.Cin) dx[((size_t)n * d.Cin + ci) * g.I + pos] = acc[c] + (bias ? __ldg(bias + ci) : 0.f);
+    }
+}
+
+}  // namespace direct
+
+int maavss_conv_dgrad_direct(const maavss_conv_desc* d, const float* dy, const float* w, const float* bias, float* dx,
+                             cudaStream_t st) {
+    direct::Geo g = direct::make_geo(d);
+    const long long Q = (long long)d->N * g.I;
+    // channels per thread: 16 when that still gives every SM a CTA, fewer for the deep 8x8 / 8x4 layers
+    int CI_T = d->Cin >= 16 ? 16 : (d->Cin > 4 ? 8 : 4);
+    const int sms = maavss_num_sms();
+    while (CI_T > 4 && (long long)ceil_div(Q, direct::DG_T) * ceil_div(d->Cin, CI_T) < sms) CI_T /= 2;
+    const int co_chunk = min(d->Cout, direct::DG_WS / (g.KV * CI_T));
+    // envelope: the staged weight block must fit, and the layer must be small enough that re-reading dy per group of
+    // CI_T input channels (no shared-memory reuse of dy) is cheaper than the implicit GEMM's index work
+    const double fma = (double)Q * d->Cin * d->Cout * g.KV / ((double)d->SD * d->SH * d->SW);
+    if (co_chunk < 1 || Q >= (1LL << 31) || fma > 8e9 || ceil_div(d->Cin, CI_T) > 65535) return 0;
+    dim3 grid(ceil_div(Q, direct::DG_T), ceil_div(d->Cin, CI_T));
+    if (CI_T == 16) direct::dgrad_kernel<16><<<grid, direct::DG_T, 0, st>>>(g, dy, w, bias, dx, (int)Q, co_chunk);
+    else if (CI_T == 8) direct::dgrad_kernel<8><<<grid, direct::DG_T, 0, st>>>(g, dy, w, bias, dx, (int)Q, co_chunk);
+    else direct::dgrad_kernel<4><<<grid, direct::DG_T, 0, st>>>(g, dy, w, bias, dx, (int)Q, co_chunk);
     MAAVSS_LAUNCH_CHECK();
     return 1;
 }

@@ -352,6 +352,9 @@ int launch(igemm::Geo g, const float* a, const float* b, const float* bias, floa
 
 }  // namespace
 
+int maavss_conv_wgrad_direct(const maavss_conv_desc*, const float*, const float*, float*, int, cudaStream_t);
+int maavss_conv_dgrad_direct(const maavss_conv_desc*, const float*, const float*, const float*, float*, cudaStream_t);
+
 extern "C" int maavss_conv_fwd(const maavss_conv_desc* d, const float* x, const float* w, const float* bias, float* y, void* stream) {
     int rc = check_desc(d, "conv_fwd");
     if (rc) return rc;
@@ -369,6 +372,8 @@ extern "C" int maavss_conv_dgrad(const maavss_conv_desc* d, const float* dy, con
     if (rc) return rc;
     if (d->N == 0) return MAAVSS_OK;
     MAAVSS_CHECK_ARG(dy && w && dx, "conv_dgrad: null argument");
+    rc = maavss_conv_dgrad_direct(d, dy, w, bias, dx, (cudaStream_t)stream);
+    if (rc != 0) return rc < 0 ? rc : MAAVSS_OK;
     igemm::Geo g = make_geo(d);
     g.Mdim = d->N * g.I;
     g.Ndim = d->Cin;
@@ -386,6 +391,8 @@ extern "C" int maavss_conv_wgrad(const maavss_conv_desc* d, const float* x, cons
         if (!accumulate) MAAVSS_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * (size_t)elems, (cudaStream_t)stream));
         return MAAVSS_OK;
     }
+    rc = maavss_conv_wgrad_direct(d, x, dy, dw, accumulate, (cudaStream_t)stream);
+    if (rc != 0) return rc < 0 ? rc : MAAVSS_OK;
     g.Mdim = d->Cout;
     g.Ndim = d->Cin * g.KV;
     g.Kdim = d->N * g.O;
