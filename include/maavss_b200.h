@@ -94,6 +94,15 @@ int maavss_conv_dgrad(const maavss_conv_desc* d, const float* dy, const float* w
 /* dw (+)= sum over batch/positions of dy (x) x.   accumulate != 0 adds into dw (gradient accumulation over num_seq,
  * train.py:158), else dw is overwritten. */
 int maavss_conv_wgrad(const maavss_conv_desc* d, const float* x, const float* dy, float* dw, int accumulate, void* stream);
+/* Tensor-core (tcgen05 + TMA, bf16 operands, fp32 accumulate) variant of maavss_conv_fwd (mode 0: act = x, out = y) and
+ * maavss_conv_dgrad (mode 1: act = dy, out = dx) for the stride-1 "same" Conv3d / Conv2d layers of the
+ * AV_Fusion_Model_Frames visual encoder (nn.Conv3d(k=(3,5,5), bias=False), avse_model_final.py:33-59): channels in
+ * {16, 32, 64}, W in {32, 64, 128}, H a multiple of 128 / W.  No bias.  workspace (caller-owned, 1024-byte aligned,
+ * maavss_conv_tc_workspace_bytes) holds the channels-last bf16 copy of act and the repacked weights. */
+int maavss_conv_tc_supported(const maavss_conv_desc* d, int mode);
+long long maavss_conv_tc_workspace_bytes(const maavss_conv_desc* d, int mode);
+int maavss_conv_tc(const maavss_conv_desc* d, int mode, const float* act, const float* w, float* out, void* workspace,
+                   long long workspace_bytes, void* stream);
 /* out[c] (+)= sum_{n,i} x[n, c, i]   (bias gradients). workspace: maavss_reduce_workspace_bytes(C). */
 int maavss_channel_sum(const float* x, int N, int C, long long inner, float* out, int accumulate, void* workspace, void* stream);
 int maavss_reduce_workspace_bytes(int C);

@@ -69,6 +69,24 @@ def channel_sum(x5, out, accumulate):
     check(lib().maavss_channel_sum(fptr(x5), N, C, inner, fptr(out), accumulate, dptr(ws), stream_ptr()))
 
 
+# Tensor-core (tcgen05, bf16 operands / fp32 accumulate) path for the stride-1 "same" Conv3d / Conv2d layers with
+# 16 / 32 / 64 channels (the visual encoder of AV_Fusion_Model_Frames): off by default so that the fp32 parity
+# tolerances of the model tests hold; the Frames train step / benchmark switch it on (tolerance 2e-2).
+TENSOR_CORE_CONV = False
+
+
+def _conv_tc(desc, mode, act5, w5, out5):
+    """Returns True when the layer ran on the tensor-core kernel."""
+    if not TENSOR_CORE_CONV or not lib().maavss_conv_tc_supported(ctypes.byref(desc), mode):
+        return False
+    nbytes = lib().maavss_conv_tc_workspace_bytes(ctypes.byref(desc), mode)
+    ws = torch.empty(nbytes + 1024, device=act5.device, dtype=torch.uint8)
+    off = (-ws.data_ptr()) % 1024
+    check(lib().maavss_conv_tc(ctypes.byref(desc), mode, fptr(act5), fptr(w5), fptr(out5), ctypes.c_void_p(ws.data_ptr() + off),
+                               ctypes.c_longlong(nbytes), stream_ptr()))
+    return True
+
+
 class ConvFn(torch.autograd.Function):
     """nn.Conv2d / nn.Conv3d forward + backward (zero padding, no dilation / groups)."""
 
@@ -80,7 +98,8 @@ class ConvFn(torch.autograd.Function):
         out3 = tuple((x5.shape[2 + i] + 2 * p[i] - w5.shape[2 + i]) // s[i] + 1 for i in range(3))
         desc = make_conv_desc(x5.shape, w5.shape, s, p, out3)
         y = torch.empty((x5.shape[0], w5.shape[0]) + out3, device=x.device, dtype=torch.float32)
-        check(lib().maavss_conv_fwd(ctypes.byref(desc), fptr(x5), fptr(w5.contiguous()), _opt(bias), fptr(y), stream_ptr()))
+        if bias is not None or not _conv_tc(desc, 0, x5, w5.contiguous(), y):
+            check(lib().maavss_conv_fwd(ctypes.byref(desc), fptr(x5), fptr(w5.contiguous()), _opt(bias), fptr(y), stream_ptr()))
         ctx.desc, ctx.nd = desc, nd
         ctx.save_for_backward(x5, weight, bias)
         return y if nd == 5 else y.squeeze(2)
@@ -93,7 +112,8 @@ class ConvFn(torch.autograd.Function):
         dx = gw = gb = None
         if ctx.needs_input_grad[0]:
             dx5 = torch.empty_like(x5)
-            check(lib().maavss_conv_dgrad(ctypes.byref(desc), fptr(dy5), fptr(weight), _null(), fptr(dx5), stream_ptr()))
+            if not _conv_tc(desc, 1, dy5, _as5(weight).contiguous(), dx5):
+                check(lib().maavss_conv_dgrad(ctypes.byref(desc), fptr(dy5), fptr(weight), _null(), fptr(dx5), stream_ptr()))
             dx = dx5 if ctx.nd == 5 else dx5.squeeze(2)
         tgt, acc, gw = _grad_slot(weight, ctx.needs_input_grad[1])
         if tgt is not None:

@@ -235,3 +235,41 @@ def test_maxpool3d(shape, pk):
     yo.backward(dy)
     yr.backward(dy)
     assert torch.equal(xo.grad, xr.grad)
+
+
+@pytest.mark.parametrize("N,Cin,Cout,D,H,W,k,p", [
+    (2, 16, 32, 3, 16, 128, (3, 5, 5), (1, 2, 2)),      # visual encoder layer 2 geometry (avse_model_final.py:39)
+    (3, 32, 64, 2, 8, 64, (3, 5, 5), (1, 2, 2)),
+    (2, 64, 64, 4, 8, 32, (3, 5, 5), (1, 2, 2)),
+    (1, 64, 16, 1, 4, 32, (1, 3, 3), (0, 1, 1)),
+    (5, 16, 16, 2, 2, 64, (3, 1, 5), (1, 0, 2)),
+])
+def test_conv_tensor_core(N, Cin, Cout, D, H, W, k, p):
+    """tcgen05 implicit-GEMM convolution (forward and data gradient) vs torch on the same bf16-rounded operands
+    (tight: only the accumulation order differs) and vs the fp32 result (bf16-operand tolerance 2e-2)."""
+    from maavss_b200 import nn_ops as ops
+    x = torch.randn(N, Cin, D, H, W, generator=g(31)).cuda()
+    w = (torch.randn(Cout, Cin, *k, generator=g(32)) / (Cin * k[0] * k[1] * k[2]) ** 0.5).cuda()
+    dy = torch.randn(N, Cout, D, H, W, generator=g(33)).cuda()
+    xr, wr, dyr = (t.to(torch.bfloat16).float() for t in (x, w, dy))
+    ops.TENSOR_CORE_CONV = True
+    try:
+        xo = x.clone().requires_grad_()
+        wo = w.clone().requires_grad_()
+        yo = ops.conv(xo, wo, None, (1, 1, 1), p)
+        yo.backward(dy)
+    finally:
+        ops.TENSOR_CORE_CONV = False
+    xb = xr.clone().requires_grad_()
+    yb = F.conv3d(xb, wr, None, 1, p)
+    assert rel_err(yo, yb) < 2e-5
+    assert rel_err(yo, F.conv3d(x, w, None, 1, p)) < 2e-2
+    dxb = torch.autograd.grad(F.conv3d(xb, wr, None, 1, p), xb, dyr)[0]
+    assert rel_err(xo.grad, dxb) < 2e-5
+    x32 = x.clone().requires_grad_()
+    dx32 = torch.autograd.grad(F.conv3d(x32, w, None, 1, p), x32, dy)[0]
+    assert rel_err(xo.grad, dx32) < 2e-2
+    # the weight gradient stays on the fp32 path
+    w32 = w.clone().requires_grad_()
+    dw32 = torch.autograd.grad(F.conv3d(x, w32, None, 1, p), w32, dy)[0]
+    assert rel_err(wo.grad, dw32) < 2e-5
