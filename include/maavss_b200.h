@@ -103,6 +103,12 @@ int maavss_conv_tc_supported(const maavss_conv_desc* d, int mode);
 long long maavss_conv_tc_workspace_bytes(const maavss_conv_desc* d, int mode);
 int maavss_conv_tc(const maavss_conv_desc* d, int mode, const float* act, const float* w, float* out, void* workspace,
                    long long workspace_bytes, void* stream);
+/* Tensor-core variant of maavss_conv_wgrad for the same layer envelope (Cout in {16, 32, 64}): both operands are read
+ * MN-major from channels-last bf16 copies in the workspace; partial sums meet in dw through atomicAdd. */
+int maavss_conv_wgrad_tc_supported(const maavss_conv_desc* d);
+long long maavss_conv_wgrad_tc_workspace_bytes(const maavss_conv_desc* d);
+int maavss_conv_wgrad_tc(const maavss_conv_desc* d, const float* x, const float* dy, float* dw, int accumulate, void* workspace,
+                         long long workspace_bytes, void* stream);
 /* out[c] (+)= sum_{n,i} x[n, c, i]   (bias gradients). workspace: maavss_reduce_workspace_bytes(C). */
 int maavss_channel_sum(const float* x, int N, int C, long long inner, float* out, int accumulate, void* workspace, void* stream);
 int maavss_reduce_workspace_bytes(int C);

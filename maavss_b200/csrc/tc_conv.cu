@@ -163,14 +163,17 @@ __global__ void __launch_bounds__(THREADS, 1) tc_conv_kernel(const __grid_consta
 
 // (N, C, S) fp32 -> (N, S, C) bf16.  A thread gathers the C channels of one position (coalesced across the warp for
 // every channel) and writes them as C/8 16-byte vectors.
-template <int C>
+// CP >= C pads every position with zero channels (the weight-gradient kernel wants 64-channel dy rows).
+template <int C, int CP = C>
 __global__ void __launch_bounds__(256) to_channels_last_bf16(const float* __restrict__ x, __nv_bfloat16* __restrict__ out,
                                                              long long S, long long total) {
     const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= total) return;
     const long long n = e / S, s = e - n * S;
     const float* src = x + (size_t)n * C * S + s;
-    uint4* dst = reinterpret_cast<uint4*>(out + (size_t)e * C);
+    uint4* dst = reinterpret_cast<uint4*>(out + (size_t)e * CP);
+#pragma unroll
+    for (int c8 = C / 8; c8 < CP / 8; ++c8) dst[c8] = make_uint4(0u, 0u, 0u, 0u);
 #pragma unroll
     for (int c8 = 0; c8 < C / 8; ++c8) {
         uint32_t w[4];
@@ -197,7 +200,25 @@ __global__ void repack_weights_bf16(const float* __restrict__ w, __nv_bfloat16* 
     }
 }
 
+
 }  // namespace tcc
+
+// (N, C, S) fp32 -> (N, S, CP) bf16 with zero channels C..CP (shared with tc_conv_wgrad.cu)
+int maavss_tc_to_channels_last(const float* x, void* out, int C, int CP, long long S, long long total, cudaStream_t st) {
+    __nv_bfloat16* o = (__nv_bfloat16*)out;
+    const int blocks = ceil_div(total, 256);
+    if (C == 16 && CP == 16) tcc::to_channels_last_bf16<16, 16><<<blocks, 256, 0, st>>>(x, o, S, total);
+    else if (C == 32 && CP == 32) tcc::to_channels_last_bf16<32, 32><<<blocks, 256, 0, st>>>(x, o, S, total);
+    else if (C == 64 && CP == 64) tcc::to_channels_last_bf16<64, 64><<<blocks, 256, 0, st>>>(x, o, S, total);
+    else if (C == 16 && CP == 64) tcc::to_channels_last_bf16<16, 64><<<blocks, 256, 0, st>>>(x, o, S, total);
+    else if (C == 32 && CP == 64) tcc::to_channels_last_bf16<32, 64><<<blocks, 256, 0, st>>>(x, o, S, total);
+    else {
+        maavss_set_error("tc_to_channels_last: unsupported channel counts %d -> %d", C, CP);
+        return MAAVSS_ERR_UNSUPPORTED;
+    }
+    MAAVSS_LAUNCH_CHECK();
+    return MAAVSS_OK;
+}
 
 // ------------------------------------------------------------------------------------------------ host side
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -271,11 +292,10 @@ extern "C" int maavss_conv_tc(const maavss_conv_desc* d, int mode, const float* 
     const long long S = (long long)g.D * g.H * g.W, total = S * g.N;
     __nv_bfloat16* act_cl = (__nv_bfloat16*)workspace;
     __nv_bfloat16* w_rp = (__nv_bfloat16*)((uint8_t*)workspace + align_up((size_t)total * g.Ca * 2, 1024));
-    const int blocks = ceil_div(total, 256);
-    if (g.Ca == 16) tcc::to_channels_last_bf16<16><<<blocks, 256, 0, st>>>(act, act_cl, S, total);
-    else if (g.Ca == 32) tcc::to_channels_last_bf16<32><<<blocks, 256, 0, st>>>(act, act_cl, S, total);
-    else tcc::to_channels_last_bf16<64><<<blocks, 256, 0, st>>>(act, act_cl, S, total);
-    MAAVSS_LAUNCH_CHECK();
+    {
+        const int rc = maavss_tc_to_channels_last(act, act_cl, g.Ca, g.Ca, S, total, st);
+        if (rc) return rc;
+    }
     tcc::repack_weights_bf16<<<ceil_div(d->Cout * d->Cin * KV, 256), 256, 0, st>>>(w, w_rp, d->Cout, d->Cin, KV, mode);
     MAAVSS_LAUNCH_CHECK();
 

@@ -87,6 +87,17 @@ def _conv_tc(desc, mode, act5, w5, out5):
     return True
 
 
+def _conv_wgrad_tc(desc, x5, dy5, tgt, acc):
+    if not TENSOR_CORE_CONV or not lib().maavss_conv_wgrad_tc_supported(ctypes.byref(desc)):
+        return False
+    nbytes = lib().maavss_conv_wgrad_tc_workspace_bytes(ctypes.byref(desc))
+    ws = torch.empty(nbytes + 1024, device=x5.device, dtype=torch.uint8)
+    off = (-ws.data_ptr()) % 1024
+    check(lib().maavss_conv_wgrad_tc(ctypes.byref(desc), fptr(x5), fptr(dy5), fptr(tgt), acc, ctypes.c_void_p(ws.data_ptr() + off),
+                                     ctypes.c_longlong(nbytes), stream_ptr()))
+    return True
+
+
 class ConvFn(torch.autograd.Function):
     """nn.Conv2d / nn.Conv3d forward + backward (zero padding, no dilation / groups)."""
 
@@ -116,7 +127,7 @@ class ConvFn(torch.autograd.Function):
                 check(lib().maavss_conv_dgrad(ctypes.byref(desc), fptr(dy5), fptr(weight), _null(), fptr(dx5), stream_ptr()))
             dx = dx5 if ctx.nd == 5 else dx5.squeeze(2)
         tgt, acc, gw = _grad_slot(weight, ctx.needs_input_grad[1])
-        if tgt is not None:
+        if tgt is not None and not _conv_wgrad_tc(desc, x5, dy5, tgt, acc):
             check(lib().maavss_conv_wgrad(ctypes.byref(desc), fptr(x5), fptr(dy5), fptr(tgt), acc, stream_ptr()))
         if bias is not None:
             tgt, acc, gb = _grad_slot(bias, ctx.needs_input_grad[2])

@@ -269,7 +269,16 @@ def test_conv_tensor_core(N, Cin, Cout, D, H, W, k, p):
     x32 = x.clone().requires_grad_()
     dx32 = torch.autograd.grad(F.conv3d(x32, w, None, 1, p), x32, dy)[0]
     assert rel_err(xo.grad, dx32) < 2e-2
-    # the weight gradient stays on the fp32 path
+    wb = wr.clone().requires_grad_()
+    dwb = torch.autograd.grad(F.conv3d(xr, wb, None, 1, p), wb, dyr)[0]
+    assert rel_err(wo.grad, dwb) < 5e-5
     w32 = w.clone().requires_grad_()
     dw32 = torch.autograd.grad(F.conv3d(x, w32, None, 1, p), w32, dy)[0]
-    assert rel_err(wo.grad, dw32) < 2e-5
+    assert rel_err(wo.grad, dw32) < 2e-2
+    # a second backward accumulates into .grad (gradient accumulation over num_seq)
+    ops.TENSOR_CORE_CONV = True
+    try:
+        ops.conv(xo, wo, None, (1, 1, 1), p).backward(dy)
+    finally:
+        ops.TENSOR_CORE_CONV = False
+    assert rel_err(wo.grad, 2 * dwb) < 5e-5
