@@ -80,7 +80,7 @@ def main():
     tf = GFLOP_PER_CLIP_WINDOW * 4 * B / ms      # GFLOP / ms == TFLOP/s, per GPU
     line = {"metric": "AV_Fusion_Model_Frames train clips/sec", "value": round(world * B / (ms / 1e3), 2), "unit": "clips/s",
             "n_gpus": world, "clips_per_gpu": B, "global_batch": world * B, "ms_per_step": round(ms, 2), "steps": a.steps,
-            "dtype": "bf16 operands / f32 accumulate on tcgen05 for Conv3d fwd + dgrad, f32 elsewhere" if a.tc else "f32 (SIMT implicit-GEMM convolutions)", "achieved_tflops_per_gpu": round(tf, 2),
+            "dtype": "bf16 operands / f32 accumulate on tcgen05 for the Conv3d layers 2-4 (fwd, dgrad, wgrad), f32 elsewhere" if a.tc else "f32 (SIMT implicit-GEMM convolutions)", "achieved_tflops_per_gpu": round(tf, 2),
             "frac_of_bf16_tensor_peak": round(tf / pk["bf16_tflops_sustained"], 4), "execution": "eager", "sync_bn": world > 1,
             "final_loss": float(out[0]),
             "shares": {k: round(v[0] / tot, 4) for k, v in sorted(agg.items(), key=lambda kv: -kv[1][0])[:10]}}

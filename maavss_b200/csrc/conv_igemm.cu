@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(256) conv_igemm_kernel(Geo g, const float* __r
     constexpr int RM = TM / TI, RN = TN / TJ;          // per-thread micro tile
     static_assert(TM % TI == 0 && TN % TJ == 0 && 256 % TM == 0 && 256 % TN == 0, "bad tile");
     const maavss_conv_desc& d = g.d;
-    const int i0 = blockIdx.y * TM, j0 = blockIdx.x * TN;
+    const int i0 = blockIdx.x * TM, j0 = blockIdx.y * TN;     // rows on grid.x: N * positions can exceed the 65535 limit of grid.y
     const int ti = threadIdx.x % TI, tj = threadIdx.x / TI;
     const int l_begin = blockIdx.z * g.k_per_split;
     const int l_end = min(g.Kdim, l_begin + g.k_per_split);
@@ -336,7 +336,7 @@ int launch(igemm::Geo g, const float* a, const float* b, const float* bias, floa
             MAAVSS_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * (size_t)out_elems, st));
         }
     }
-    dim3 grid(ceil_div(g.Ndim, TNv), ceil_div(g.Mdim, TMv), splits);
+    dim3 grid(ceil_div(g.Mdim, TMv), ceil_div(g.Ndim, TNv), splits);
     MAAVSS_CHECK_ARG(grid.y <= 65535 && grid.z <= 65535, "conv: grid too large");
     switch (cfg) {
         case 0: igemm::conv_igemm_kernel<MODE, 64, 64, 16><<<grid, 256, 0, st>>>(g, a, b, bias, out, accumulate); break;
