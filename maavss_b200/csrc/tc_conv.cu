@@ -18,14 +18,15 @@
 
 namespace tcc {
 
-constexpr int BM = 128, STAGES = 6, ACC_STAGES = 2, THREADS = 192, TMEM_COLS = 128;
+constexpr int BM = 128, MAX_STAGES = 32, ACC_STAGES = 2, THREADS = 192, TMEM_COLS = 128;
+constexpr int SMEM_BUDGET = 150 * 1024;      // operand ring (6 stages of 24 KB at Cin = Cout = 64; a 200 KB / 32-stage ring measured no faster: the kernel is bound by L2->SM operand traffic, not by TMA latency)
 
 struct Params {
     int N, D, H, W;            // spatial extents (input == output: stride 1, "same" geometry)
     int Ca, Co;                // reduction channels (operand A / B rows of C) and output channels
     int KD, KH, KW, PD, PH, PW;
     int BH, log2BW;            // tile = BH rows x BW (= W) columns = 128 positions
-    int a_bytes, stage_bytes, swz;
+    int a_bytes, stage_bytes, swz, stages;
     float* out;                // (N, Co, D, H, W) fp32
 };
 
@@ -51,9 +52,10 @@ __global__ void __launch_bounds__(THREADS, 1) tc_conv_kernel(const __grid_consta
                                                              const __grid_constant__ CUtensorMap tmB, Params p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
+    const int STAGES = p.stages;
     uint64_t* full = (uint64_t*)(smem + STAGES * p.stage_bytes);
-    uint64_t* empty = full + STAGES;
-    uint64_t* tfull = empty + STAGES;
+    uint64_t* empty = full + MAX_STAGES;
+    uint64_t* tfull = empty + MAX_STAGES;
     uint64_t* tempty = tfull + ACC_STAGES;
     uint32_t* tmem_slot = (uint32_t*)(tempty + ACC_STAGES);
 
@@ -334,10 +336,12 @@ extern "C" int maavss_conv_tc(const maavss_conv_desc* d, int mode, const float* 
     p.a_bytes = 128 * swz;
     p.stage_bytes = (int)align_up((size_t)p.a_bytes + (size_t)g.Co * swz, 1024);
     p.out = out;
-    const int smem = tcc::STAGES * p.stage_bytes + 256 + 1024;
+    p.stages = tcc::SMEM_BUDGET / p.stage_bytes;
+    if (p.stages > tcc::MAX_STAGES) p.stages = tcc::MAX_STAGES;
+    const int smem = p.stages * p.stage_bytes + 1024 + 1024;       // ring + barriers / TMEM slot + alignment slack
     static bool attr_set = false;
     if (!attr_set) {
-        MAAVSS_CUDA(cudaFuncSetAttribute(tcc::tc_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tcc::STAGES * (16384 + 8192) + 256 + 1024));
+        MAAVSS_CUDA(cudaFuncSetAttribute(tcc::tc_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tcc::SMEM_BUDGET + 2048));
         attr_set = true;
     }
     const int tiles = g.N * g.D * (g.H / BH);

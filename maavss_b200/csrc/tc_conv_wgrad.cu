@@ -15,7 +15,8 @@
 
 namespace tcw {
 
-constexpr int THREADS = 192, B_STAGES = 6, A_STAGES = 2, A_BYTES = 128 * 128, B_MAX = 128 * 128;
+constexpr int THREADS = 192, MAX_B_STAGES = 32, A_STAGES = 2, A_BYTES = 128 * 128;
+constexpr int SMEM_BUDGET = 150 * 1024;      // A ring (2 x 16 KB) + B ring (deeper rings measured no faster)
 
 struct Params {
     int N, D, H, W;
@@ -24,6 +25,7 @@ struct Params {
     int BH, TG;                // tile rows; taps per CTA
     int tiles, tiles_per_cta;
     int swz_b;                 // bytes of one x row = 2 * Cin
+    int b_stages;              // depth of the B ring (tiles of 128 * swz_b bytes)
     int lane_layout;           // TMEM lane of accumulator row r for M = 64: 0 -> r, 1 -> 32 * (r / 16) + r % 16
     float* dw;                 // (Cout, Cin, KV) fp32, accumulated into
 };
@@ -52,12 +54,14 @@ __global__ void __launch_bounds__(THREADS, 1) tc_conv_wgrad_kernel(const __grid_
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* a_buf = smem;                                   // A_STAGES x 16 KB
-    uint8_t* b_buf = smem + A_STAGES * A_BYTES;              // B_STAGES x 16 KB
+    uint8_t* b_buf = smem + A_STAGES * A_BYTES;              // b_stages x (128 * swz_b) bytes
+    const int B_STAGES = p.b_stages;
+    const int B_MAX = 128 * p.swz_b;
     uint64_t* a_full = (uint64_t*)(b_buf + B_STAGES * B_MAX);
     uint64_t* a_empty = a_full + A_STAGES;
     uint64_t* b_full = a_empty + A_STAGES;
-    uint64_t* b_empty = b_full + B_STAGES;
-    uint64_t* tfull = b_empty + B_STAGES;
+    uint64_t* b_empty = b_full + MAX_B_STAGES;
+    uint64_t* tfull = b_empty + MAX_B_STAGES;
     uint32_t* tmem_slot = (uint32_t*)(tfull + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -260,10 +264,12 @@ extern "C" int maavss_conv_wgrad_tc(const maavss_conv_desc* d, const float* x, c
     p.swz_b = d->Cin * 2;
     p.lane_layout = 1;      // verified on B200: an M = 64 accumulator keeps row r in lane 32 * (r / 16) + r % 16
     p.dw = dw;
-    const int smem = (tcw::A_STAGES + tcw::B_STAGES) * tcw::A_BYTES + 256 + 1024;
+    p.b_stages = (tcw::SMEM_BUDGET - tcw::A_STAGES * tcw::A_BYTES) / (128 * p.swz_b);
+    if (p.b_stages > tcw::MAX_B_STAGES) p.b_stages = tcw::MAX_B_STAGES;
+    const int smem = tcw::A_STAGES * tcw::A_BYTES + p.b_stages * 128 * p.swz_b + 1024 + 1024;
     static bool attr_set = false;
     if (!attr_set) {
-        MAAVSS_CUDA(cudaFuncSetAttribute(tcw::tc_conv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        MAAVSS_CUDA(cudaFuncSetAttribute(tcw::tc_conv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tcw::SMEM_BUDGET + 2048));
         attr_set = true;
     }
     tcw::tc_conv_wgrad_kernel<<<dim3(chunks, groups), tcw::THREADS, smem, st>>>(tmDy, tmX, p);
