@@ -337,9 +337,14 @@ def run_ours(args):
         top = sorted(agg.items(), key=lambda kv: -kv[1][0])
         (name, tag), (ms_sum, calls, nbytes) = top[0]
         achieved = (nbytes / (ms_sum / calls * 1e-3) / 1e9) if nbytes else None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(f"{name}[{tag}]")
+        except Exception:
+            traffic = None
         line["roofline"] = {"bound": "hbm", "kernel": f"{name}[{tag}]", "achieved": round(achieved, 1) if achieved else None,
                             "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": round(achieved / pk["hbm_gbs"], 4) if achieved else None,
-                            "traffic": None, "peak_source": pk_kind + " (MEASURED_PEAKS.json hbm_gbs)" if pk_kind == "measured" else "fallback",
+                            "traffic": traffic, "traffic_source": "profiles/ncu_traffic.json (ncu --set full, dram read + write per launch)" if traffic else None,
+                            "algorithmic_bytes": nbytes, "peak_source": pk_kind + " (MEASURED_PEAKS.json hbm_gbs)" if pk_kind == "measured" else "fallback",
                             "share_of_step": round(ms_sum / tot, 4), "avg_ms": round(ms_sum / calls, 5), "calls_per_step": calls // 3,
                             "how": "CUDA events around each C-ABI call of one eager (non-graph) step, 3 repetitions"}
         line["kernel_breakdown"] = [{"call": f"{n}[{t}]", "share": round(e[0] / tot, 4), "avg_ms": round(e[0] / e[1], 5),

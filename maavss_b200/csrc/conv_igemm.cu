@@ -314,6 +314,9 @@ int launch(igemm::Geo g, const float* a, const float* b, const float* bias, floa
     else if (g.Ndim <= 16) { cfg = 3; TMv = 128; TNv = 16; }
     else if (g.Mdim <= 8) { cfg = 4; TMv = 8; TNv = 256; }
     else if (g.Mdim <= 16) { cfg = 5; TMv = 16; TNv = 128; }
+    // the weight gradient gets its parallelism from splitting the (huge) position reduction, not from small tiles:
+    // 64 x 64 tiles keep 16 FMAs per 8 shared-memory loads (ncu: the 32 x 32 tiles ran at 31 % issue-active)
+    else if (MODE == igemm::WGRAD && g.Mdim >= 48 && g.Ndim >= 48) { cfg = 0; TMv = 64; TNv = 64; }
     else if (t64 < sms) { cfg = 1; TMv = 32; TNv = 32; }
     else { cfg = 0; TMv = 64; TNv = 64; }
     const long long tiles = (long long)ceil_div(g.Mdim, TMv) * ceil_div(g.Ndim, TNv);

@@ -216,7 +216,9 @@ def test_sub_forwards_and_toggles():
             assert p.grad is None, k
         else:
             scale = max(float(q.grad.abs().max()), 1e-12)
-            assert float((p.grad.cpu() - q.grad).abs().max()) < 2e-4 * scale + 1e-7, k   # 1e-7: zero-gradient conv biases hold noise
+            # 1e-6: the conv biases in front of a train-mode BatchNorm have an exactly-zero gradient; both sides hold
+            # summation noise ~ eps * sum|dy| there, and ours depends on the atomicAdd order of the split reductions
+            assert float((p.grad.cpu() - q.grad).abs().max()) < 2e-4 * scale + 1e-6, k
     m.toggle_enc_grads(False)
     assert not any(p.requires_grad for p in m.stft_encoder.parameters())
     assert all(p.requires_grad for p in m.fc1.parameters())
