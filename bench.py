@@ -304,7 +304,7 @@ def run_ours(args):
             "config": {"workload": WORKLOAD, "clips_per_gpu": B, "global_batch": world * B, "parallelism": f"dp{world}",
                        "num_seq": NUM_SEQ, "n_fft": N_FFT, "hop": ds.hop, "execution": "eager" if args.eager else "cuda-graph",
                        "l2": f"inputs rotate over {n_sets} batches ({n_sets * h2d / 1e6:.0f} MB) + 147 MB weights + optimizer arenas > 126 MB L2",
-                       "sync_bn": world > 1},
+                       "sync_bn": world > 1, "grad_allreduce": ("overlapped with the encoder backward" if step.early is not None else "after backward") if world > 1 else None},
             "clocks": clk,
             "e2e": {"value": round(world * B * args.steps / (ms_e2e / 1e3), 2), "unit": "clips/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": 12, "ms_per_step": round(ms_e2e / args.steps, 4)},
@@ -321,7 +321,7 @@ def run_ours(args):
     if True:
         pk, pk_kind = peaks()
         prof_step = train_step.FusionTrainStep(model, opt, num_seq=NUM_SEQ, num_frames=NUM_FRAMES, hops_per_frame=HOPS_PER_FRAME,
-                                               p_size=64, loss_coeff=LOSS_COEFF, graph=False)
+                                               p_size=64, loss_coeff=LOSS_COEFF, graph=False, overlap_allreduce=False)
         agg = {}
         for rep in range(3):
             _lib.start_profile()

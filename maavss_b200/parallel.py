@@ -66,6 +66,42 @@ def allreduce_gradients(optimizer):
     optimizer.grad_scale = 1.0 / _WORLD
 
 
+class EarlyGradAllReduce:
+    """Overlap most of the gradient exchange with the rest of the backward pass.
+
+    The flat gradient arena is split at `offset`: everything from `offset` on (the LSTM / fc / head weights of the
+    fusion models, 98 % of the parameters, whose gradients are final once the LSTM backward has run) is all-reduced on a
+    side stream as soon as `start()` is called from an autograd hook, while the convolutional encoders are still
+    back-propagating on the main stream; `finish()` reduces the head of the arena and joins the side stream.  Both
+    streams' work is captured when the step is recorded into a CUDA graph."""
+
+    def __init__(self, optimizer, offset):
+        self.opt, self.offset = optimizer, int(offset)
+        self.side = torch.cuda.Stream() if _GROUP is not None else None
+        self.started = False
+
+    def start(self):
+        if _GROUP is None or self.started:
+            return
+        self.started = True
+        self.side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self.side):
+            dist.all_reduce(self.opt.flat.grad[self.offset:], op=dist.ReduceOp.SUM, group=_GROUP)
+
+    def finish(self):
+        if _GROUP is None:
+            return
+        g = self.opt.flat.grad
+        if self.started:
+            if self.offset > 0:
+                dist.all_reduce(g[:self.offset], op=dist.ReduceOp.SUM, group=_GROUP)
+            torch.cuda.current_stream().wait_stream(self.side)
+        else:
+            dist.all_reduce(g, op=dist.ReduceOp.SUM, group=_GROUP)
+        self.started = False
+        self.opt.grad_scale = 1.0 / _WORLD
+
+
 def allreduce_max_(t):
     if _GROUP is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=_GROUP)

@@ -25,9 +25,20 @@ class _TrainStepBase:
     def micro_steps(self, *inputs):
         raise NotImplementedError
 
+    early = None      # parallel.EarlyGradAllReduce, set by subclasses that know where the arena can be split
+
+    _running = False
+
     def _eager(self, *inputs):
-        out = self.micro_steps(*inputs)
-        parallel.allreduce_gradients(self.opt)
+        self._running = True          # the LSTM hook of another step object built on the same model stays quiet
+        try:
+            out = self.micro_steps(*inputs)
+        finally:
+            self._running = False
+        if self.early is not None:
+            self.early.finish()
+        else:
+            parallel.allreduce_gradients(self.opt)
         self.opt.step()
         self.opt.zero_grad()
         return out
@@ -73,10 +84,30 @@ class FusionTrainStep(_TrainStepBase):
     streamed from HBM once per optimizer step instead of num_seq times and the launch count drops by num_seq."""
 
     def __init__(self, model, optimizer, num_seq=4, num_frames=8, hops_per_frame=8, p_size=64, loss_coeff=0.001,
-                 batch_windows=True, **kw):
+                 batch_windows=True, overlap_allreduce=True, **kw):
         super().__init__(model, optimizer, **kw)
         self.num_seq, self.num_frames, self.hpf, self.p_size, self.loss_coeff = num_seq, num_frames, hops_per_frame, p_size, loss_coeff
         self.batch_windows = batch_windows
+        self._setup_early_allreduce(overlap_allreduce)
+
+    def _setup_early_allreduce(self, enabled):
+        """avse_model.AV_Fusion_Model.forward trains [encoders | lstm fc1 fc2 (decoders: unused) a_fc1 v_fc1]: from the
+        first LSTM weight to the end of the arena nothing receives gradient after the LSTM backward, so that tail is
+        exchanged while the encoders back-propagate (the hook fires when the LSTM's input gradient exists)."""
+        m = self.model
+        if not enabled or parallel.world_size() == 1 or getattr(m, "VARIANT", None) != "fc" or not self.batch_windows:
+            return
+        first = next(m.lstm.parameters())
+        flat = self.opt.flat
+        if id(first) not in flat.index:
+            return
+        self.early = parallel.EarlyGradAllReduce(self.opt, flat.offsets[flat.index[id(first)]])
+
+        def pre_hook(mod, args):
+            x = args[0]
+            if torch.is_tensor(x) and x.requires_grad:
+                x.register_hook(lambda g: (self.early.start() if self._running else None, None)[1])
+        m.lstm.register_forward_pre_hook(pre_hook)
 
     def _windows_batched(self, x_stft, y_stft, attn):
         G, B = self.num_seq, x_stft.shape[0]
