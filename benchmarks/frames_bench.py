@@ -45,7 +45,7 @@ def main():
     parallel.broadcast_module(model)
     model.train()
     opt = optim.Adam(model.parameters(), lr=1e-5)
-    step = train_step.FramesTrainStep(model, opt, num_seq=4, num_frames=8, hops_per_frame=8, loss_coeff=0.001, graph=False)
+    step = train_step.FramesTrainStep(model, opt, num_seq=4, num_frames=8, hops_per_frame=8, loss_coeff=0.001, graph=False, tensor_core=bool(a.tc))
     g = torch.Generator().manual_seed(1234 + rank)
     y = torch.randn(B, 2, 96, 129, generator=g).to(dev)
     x = y + 0.1 * torch.randn(B, 2, 96, 129, generator=g).to(dev)
