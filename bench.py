@@ -173,6 +173,19 @@ def algorithmic_bytes(name, a):
         k = {"maavss_bn_apply_act": (4, 2), "maavss_bn_bwd_apply": (6, 4), "maavss_bn_reduce": (1, 1), "maavss_bn_bwd_reduce": (4, 3)}[name]
         N, C, inner = iv(a[k[0]]), iv(a[k[0] + 1]), iv(a[k[0] + 2])
         return 4 * k[1] * N * C * inner, f"N{N} C{C} inner{inner}"
+    if name == "maavss_channel_sum":
+        N, C, inner = iv(a[1]), iv(a[2]), iv(a[3])
+        return 4 * (N * C * inner + C), f"N{N} C{C} inner{inner}"
+    if name in ("maavss_bn_reduce_grouped", "maavss_bn_apply_grouped", "maavss_bn_bwd_reduce_grouped", "maavss_bn_bwd_apply_grouped"):
+        # tensors of N*C*inner floats touched once each: x | x, y | dy, y, x | dy, y, x, dx
+        k = {"maavss_bn_reduce_grouped": (1, 1), "maavss_bn_apply_grouped": (2, 2), "maavss_bn_bwd_reduce_grouped": (4, 3),
+             "maavss_bn_bwd_apply_grouped": (7, 4)}[name]
+        N, C, inner = iv(a[k[0]]), iv(a[k[0] + 1]), iv(a[k[0] + 2])
+        return 4 * k[1] * N * C * inner, f"N{N} C{C} inner{inner}"
+    if name in ("maavss_lstm_step_fwd", "maavss_lstm_step_bwd"):
+        B, T, H = (iv(a[i]) for i in ((6, 7, 8) if name.endswith("fwd") else (7, 8, 9)))
+        # per direction: W_hh (4H x H), one time slice of gin / gates (B x 4H each), cells, h (B x H each)
+        return 4 * 2 * (4 * H * H + 2 * B * 4 * H + 3 * B * H), f"B{B} T{T} H{H}"
     if name == "maavss_video_phasegram":
         B, T, H, W, R = (iv(a[i]) for i in range(4, 9))
         return 4 * B * T * (H * W + R * R), f"B{B} T{T} {H}x{W}->{R}"

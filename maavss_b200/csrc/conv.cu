@@ -1,22 +1,38 @@
 // Per-channel sums (bias gradients) for the convolution layers; the convolutions themselves are in conv_igemm.cu.
+#include <stdint.h>
 #include "common.cuh"
 #include "../../include/maavss_b200.h"
 
 namespace {
 
 // out[c] (+)= sum_{n,i} x[n,c,i]; two deterministic stages through a double workspace [C][S].
+// Stage 1: CTA (s, c) walks the rows n = s, s + S, ... of channel c with float4 loads and four independent fp32 partial
+// sums per thread (no index division in the loop), then reduces in double.
 constexpr int kSumSplits = 16;
-__global__ void channel_sum_partial(const float* __restrict__ x, int N, int C, long long inner, double* __restrict__ ws) {
+__global__ void __launch_bounds__(256) channel_sum_partial(const float* __restrict__ x, int N, int C, long long inner,
+                                                           double* __restrict__ ws) {
     const int c = blockIdx.y, s = blockIdx.x;
-    const long long total = (long long)N * inner;
-    const long long chunk = (total + kSumSplits - 1) / kSumSplits;
-    const long long e0 = s * chunk, e1 = min(total, e0 + chunk);
-    float a = 0.f;
-    for (long long e = e0 + threadIdx.x; e < e1; e += blockDim.x) {
-        const long long n = e / inner, i = e - n * inner;
-        a += x[((size_t)n * C + c) * inner + i];
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    const bool vec = (inner & 3) == 0 && ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
+    // the 16 splits cover (row phase) x (inner range): few rows -> the inner axis is split instead
+    int rs = 1;
+    while (rs < kSumSplits && rs * 2 <= N) rs *= 2;
+    const int is = kSumSplits / rs, sn = s % rs, si = s / rs;
+    const long long chunk = (((inner + is - 1) / is) + 3) & ~3ll;
+    const long long i0 = min(inner, si * chunk), i1 = min(inner, i0 + chunk);
+    for (int n = sn; n < N; n += rs) {
+        const float* row = x + ((size_t)n * C + c) * inner;
+        if (vec) {
+            const float4* r4 = reinterpret_cast<const float4*>(row);
+            for (long long i = (i0 >> 2) + threadIdx.x; i < (i1 >> 2); i += 256) {
+                const float4 v = r4[i];
+                a0 += v.x; a1 += v.y; a2 += v.z; a3 += v.w;
+            }
+        } else {
+            for (long long i = i0 + threadIdx.x; i < i1; i += 256) a0 += row[i];
+        }
     }
-    double v = a;
+    double v = ((double)a0 + (double)a1) + ((double)a2 + (double)a3);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     __shared__ double sm[8];
@@ -24,7 +40,7 @@ __global__ void channel_sum_partial(const float* __restrict__ x, int N, int C, l
     __syncthreads();
     if (threadIdx.x == 0) {
         double t = 0;
-        for (int q = 0; q < (int)(blockDim.x >> 5); ++q) t += sm[q];
+        for (int q = 0; q < 8; ++q) t += sm[q];
         ws[(size_t)c * kSumSplits + s] = t;
     }
 }

@@ -3,9 +3,12 @@
 //   antialiased bilinear resize (H, W) -> (R, R), fft2, fftshift over ALL dims (batch and time axes roll too --
 //   reproduced), atan2, flatten, cumsum / (2*pi*R*R), temporal diff with a zero first frame, and
 //   division by the global max |.|.
-// Kernel 1: one CTA per frame keeps everything in shared memory (resize -> row FFTs -> column FFTs -> angle ->
-// block scan) and writes R*R floats; kernel 2: temporal diff + global abs-max; kernel 3: scale.
+// Kernel 0 (resize, HBM bound: it reads the raw frames once): one CTA per (frame, strip of output rows) stages the input
+// rows the strip needs in shared memory with coalesced float4 loads, filters horizontally, then vertically; ~1000 small
+// CTAs, 4 per SM, hide the load latency.  Kernel 1: one CTA per resized frame keeps everything in shared memory (row FFTs
+// -> column FFTs -> angle -> block scan) and writes R*R floats; kernel 2: temporal diff + global abs-max; kernel 3: scale.
 #include <math.h>
+#include <stdint.h>
 #include "common.cuh"
 #include "fft_core.cuh"
 #include "../../include/maavss_b200.h"
@@ -34,12 +37,90 @@ __device__ __forceinline__ void aa_weights(int i, int in_size, float scale, int&
         for (int j = 0; j < xsize; ++j) w[j] /= total;
 }
 
+// sum_j p[j * stride] * w[j], j ascending (ATen's order).  n is warp-uniform; the common down-scales (<= 5.5x) have at
+// most 12 taps and take the unrolled, predicated form.
+__device__ __forceinline__ float aa_filter(const float* p, int stride, const float* w, int n) {
+    float acc = p[0] * w[0];
+    if (n <= 12) {
+#pragma unroll
+        for (int j = 1; j < 12; ++j)
+            if (j < n) acc += p[j * stride] * w[j];
+    } else {
+        for (int j = 1; j < n; ++j) acc += p[j * stride] * w[j];
+    }
+    return acc;
+}
+
 struct PgArgs {
     const float* frames;   // (B, T, H, W)
     float* pflat;          // (B, T, R*R)
-    int B, T, H, W, do_resize, cumulative;
+    int B, T, H, W, cumulative;
     long long batch_stride;   // elements between consecutive clips of `frames` (>= T*H*W: a time-slice view needs no copy)
 };
+
+struct RsArgs {
+    const float* frames;   // (B, T, H, W), clips batch_stride apart
+    float* resized;        // (B*T, R, R)
+    int T, H, W, orc, rows_cap;   // orc output rows per CTA; rows_cap input rows of staging
+    long long batch_stride;
+};
+
+constexpr int kRsMaxOrc = 8;
+
+template <int R>
+__global__ void __launch_bounds__(kPgThreads) phasegram_resize_kernel(RsArgs a) {
+    extern __shared__ float smem[];
+    __shared__ float wx[R][kMaxTaps], wy[kRsMaxOrc][kMaxTaps];
+    __shared__ int xmin_s[R], xsz_s[R], ymin_s[kRsMaxOrc], ysz_s[kRsMaxOrc];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int frame = blockIdx.y, b = frame / a.T, t = frame % a.T;
+    const int o0 = blockIdx.x * a.orc, no = min(a.orc, R - o0);
+    const float* src = a.frames + (size_t)b * a.batch_stride + (size_t)t * a.H * a.W;
+    const int SW = a.W + 1, TS = R + 1;
+    float* stage = smem;                       // rows_cap x (W+1): bank-conflict free for a warp reading 32 rows of one column
+    float* tmp = smem + a.rows_cap * SW;       // rows_cap x (R+1)
+    if (tid < R) aa_weights(tid, a.W, (float)a.W / (float)R, xmin_s[tid], xsz_s[tid], wx[tid]);
+    else if (tid < R + no) aa_weights(o0 + tid - R, a.H, (float)a.H / (float)R, ymin_s[tid - R], ysz_s[tid - R], wy[tid - R]);
+    __syncthreads();
+    const int ylo = ymin_s[0];
+    const int rows = ymin_s[no - 1] + ysz_s[no - 1] - ylo;
+    if (rows > a.rows_cap) __trap();           // cannot happen: rows_cap is the analytic bound + 2 (launch_resize)
+    const float* p = src + (size_t)ylo * a.W;
+    if ((a.W & 3) == 0 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+        const int q4 = a.W >> 2, n4 = rows * q4;
+        const int sh = (q4 & (q4 - 1)) == 0 ? 31 - __clz(q4) : -1;
+        const float4* p4 = reinterpret_cast<const float4*>(p);
+        for (int f0 = tid; f0 < n4; f0 += 4 * kPgThreads) {       // four independent 16-byte loads in flight per thread
+            float4 v[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (f0 + k * kPgThreads < n4) v[k] = __ldg(p4 + f0 + k * kPgThreads);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int f = f0 + k * kPgThreads;
+                if (f < n4) {
+                    const int r = sh >= 0 ? (f >> sh) : f / q4;
+                    float* d = stage + r * SW + 4 * (f - r * q4);
+                    d[0] = v[k].x; d[1] = v[k].y; d[2] = v[k].z; d[3] = v[k].w;
+                }
+            }
+        }
+    } else {
+        for (int r = warp; r < rows; r += kPgThreads / 32)
+            for (int c = lane; c < a.W; c += 32) stage[r * SW + c] = __ldg(p + (size_t)r * a.W + c);
+    }
+    __syncthreads();
+    for (int oc = warp; oc < R; oc += kPgThreads / 32) {          // horizontal pass (last dim first, as ATen)
+        const int n = xsz_s[oc], x0 = xmin_s[oc];
+        for (int r = lane; r < rows; r += 32) tmp[r * TS + oc] = aa_filter(stage + r * SW + x0, 1, wx[oc], n);
+    }
+    __syncthreads();
+    float* dst = a.resized + ((size_t)frame * R + o0) * R;
+    for (int e = tid; e < no * R; e += kPgThreads) {              // vertical pass
+        const int ol = e / R, oc = e % R;
+        dst[e] = aa_filter(tmp + (ymin_s[ol] - ylo) * TS + oc, TS, wy[ol], ysz_s[ol]);
+    }
+}
 
 template <int R>
 __global__ void __launch_bounds__(kPgThreads) phasegram_frame_kernel(PgArgs a) {
@@ -52,9 +133,6 @@ __global__ void __launch_bounds__(kPgThreads) phasegram_frame_kernel(PgArgs a) {
     float2* tw = reinterpret_cast<float2*>(img + R * R);        // R entries exp(-2*pi*i*q/(2R))
     float2* rowbuf = tw + R;                                    // R rows  x BL
     float2* colbuf = rowbuf + R * BL;                           // R cols  x BL
-    float* tmp = reinterpret_cast<float*>(colbuf + R * BL);     // H x R horizontal pass (resize only)
-    __shared__ float wx[R][kMaxTaps], wy[R][kMaxTaps];
-    __shared__ int xmin_s[R], xsz_s[R], ymin_s[R], ysz_s[R];
     __shared__ float warp_tot[kPgThreads / 32];
 
     const int tid = threadIdx.x;
@@ -65,28 +143,7 @@ __global__ void __launch_bounds__(kPgThreads) phasegram_frame_kernel(PgArgs a) {
         sincospif(-(float)q / (float)R, &s, &c);
         tw[q] = make_float2(c, s);
     }
-    if (a.do_resize) {
-        if (tid < R) aa_weights(tid, a.W, (float)a.W / (float)R, xmin_s[tid], xsz_s[tid], wx[tid]);
-        else if (tid < 2 * R) aa_weights(tid - R, a.H, (float)a.H / (float)R, ymin_s[tid - R], ysz_s[tid - R], wy[tid - R]);
-        __syncthreads();
-        for (int e = tid; e < a.H * R; e += kPgThreads) {      // horizontal pass (last dim first, as ATen)
-            const int row = e / R, oc = e % R;
-            const float* p = src + (size_t)row * a.W + xmin_s[oc];
-            float acc = p[0] * wx[oc][0];
-            for (int j = 1; j < xsz_s[oc]; ++j) acc += p[j] * wx[oc][j];
-            tmp[e] = acc;
-        }
-        __syncthreads();
-        for (int e = tid; e < R * R; e += kPgThreads) {        // vertical pass
-            const int orow = e / R, oc = e % R;
-            const float* p = tmp + (size_t)ymin_s[orow] * R + oc;
-            float acc = p[0] * wy[orow][0];
-            for (int j = 1; j < ysz_s[orow]; ++j) acc += p[(size_t)j * R] * wy[orow][j];
-            img[e] = acc;
-        }
-    } else {
-        for (int e = tid; e < R * R; e += kPgThreads) img[e] = src[e];
-    }
+    for (int e = tid; e < R * R; e += kPgThreads) img[e] = src[e];
     __syncthreads();
     const int fi = tid / TPF, i = tid % TPF;
     // row FFTs: rowbuf[r][pad(v)] = sum_x img[r][x] e^{-2 pi i v x / R}
@@ -177,10 +234,29 @@ __global__ void __launch_bounds__(256) pg_scale_kernel(float* __restrict__ out, 
 }
 
 template <int R>
+int launch_resize(const float* frames, float* resized, int B, int T, int H, int W, long long batch_stride, cudaStream_t st) {
+    // input rows one strip of `orc` output rows touches: (orc - 1) * scale + 2 * support + 1, +2 of rounding slack
+    const float scale = (float)H / (float)R, support = scale >= 1.f ? scale : 1.f;
+    int orc = kRsMaxOrc, rows_cap = 0;
+    size_t smem = 0;
+    for (;; orc /= 2) {
+        rows_cap = (int)ceilf((orc - 1) * scale + 2.f * support) + 3;
+        if (rows_cap > H) rows_cap = H;
+        smem = sizeof(float) * (size_t)rows_cap * ((W + 1) + (R + 1));
+        if (smem <= 56 * 1024 || orc == 1) break;
+    }
+    MAAVSS_CHECK_ARG(smem + 12 * 1024 <= 227 * 1024, "video_phasegram: frame %dx%d too large for the shared-memory resize", H, W);
+    RsArgs a{frames, resized, T, H, W, orc, rows_cap, batch_stride};
+    MAAVSS_CUDA(cudaFuncSetAttribute(phasegram_resize_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    MAAVSS_CHECK_ARG((long long)B * T <= 65535, "video_phasegram: B*T > 65535");
+    phasegram_resize_kernel<R><<<dim3((R + orc - 1) / orc, B * T), kPgThreads, smem, st>>>(a);
+    MAAVSS_LAUNCH_CHECK();
+    return MAAVSS_OK;
+}
+
+template <int R>
 int launch_frames(const PgArgs& a, cudaStream_t st) {
-    size_t smem = sizeof(float) * R * R + sizeof(float2) * (R + 2 * R * fft_buf_len(R));
-    if (a.do_resize) smem += sizeof(float) * (size_t)a.H * R;
-    MAAVSS_CHECK_ARG(smem + 20 * 1024 <= 227 * 1024, "video_phasegram: frame %dx%d too large for the shared-memory resize", a.H, a.W);
+    const size_t smem = sizeof(float) * R * R + sizeof(float2) * (R + 2 * R * fft_buf_len(R));
     MAAVSS_CUDA(cudaFuncSetAttribute(phasegram_frame_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     phasegram_frame_kernel<R><<<a.B * a.T, kPgThreads, smem, st>>>(a);
     MAAVSS_LAUNCH_CHECK();
@@ -198,8 +274,14 @@ extern "C" int maavss_video_phasegram(const float* frames, float* out, float* sc
     MAAVSS_CHECK_ARG(!do_resize || (H >= R && W >= R && H <= 16 * R && W <= 16 * R), "video_phasegram: only down-scaling by <= 16 is supported");
     cudaStream_t st = (cudaStream_t)stream;
     MAAVSS_CHECK_ARG(batch_stride >= (long long)T * H * W, "video_phasegram: batch_stride smaller than one clip");
-    PgArgs a{frames, scratch, B, T, H, W, do_resize, cumulative, batch_stride};
-    int rc = launch_frames<64>(a, st);
+    int rc;
+    if (do_resize) {
+        // `out` is free until the diff / max kernel writes it: it holds the resized frames (B*T, R, R) meanwhile
+        rc = launch_resize<64>(frames, out, B, T, H, W, batch_stride, st);
+        if (rc) return rc;
+    }
+    PgArgs a{do_resize ? out : frames, scratch, B, T, R, R, cumulative, do_resize ? (long long)T * R * R : batch_stride};
+    rc = launch_frames<64>(a, st);
     if (rc) return rc;
     const long long n = (long long)R * R, total = n * B * T;
     MAAVSS_CUDA(cudaMemsetAsync(max_ws, 0, sizeof(unsigned int), st));

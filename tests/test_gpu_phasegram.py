@@ -52,3 +52,27 @@ def test_phasegram_no_resize_matches_oracle():
     ref = op.video_phasegram(fr)
     assert float((pg - ref).abs().median()) < 2e-6
     assert float(((pg - ref).abs() > 2e-3).float().mean()) < 2e-3
+
+
+@pytest.mark.parametrize("shape", [(2, 5, 100, 90), (2, 4, 130, 256), (1, 3, 300, 384), (2, 4, 66, 1000)])
+def test_phasegram_resize_paths(shape):
+    """Chunked shared-memory resize: scalar staging (W % 4 != 0), a last partial chunk (H % 32 != 0), wide rows."""
+    from maavss_b200 import utilities
+    B, T, H, W = shape
+    attn = synth.attn_clip(B, T, H, W, seed=5)
+    pg = utilities.video_phasegram(attn.cuda(), resize=(64, 64), diff=False, cumulative=False, normalize=False).cpu()
+    ref = op.video_phasegram(attn, resize=(64, 64), diff=False, cumulative=False, normalize=False)
+    assert float((pg - ref).abs().median()) < 2e-6
+    assert float(((pg - ref).abs() > 1e-4).float().mean()) < 2e-3
+
+
+def test_phasegram_time_slice_view():
+    """train.py:139 passes a time slice of the clip's attention frames: strided batch, no copy."""
+    from maavss_b200 import utilities
+    attn = synth.attn_clip(3, 12, 256, 256, seed=9)
+    view = attn.cuda()[:, :, 2:10]
+    pg = utilities.video_phasegram(view, resize=(64, 64)).cpu()
+    ref = utilities.video_phasegram(view.contiguous(), resize=(64, 64)).cpu()
+    assert torch.equal(pg, ref)
+    orc = op.video_phasegram(attn[:, :, 2:10], resize=(64, 64))
+    assert float((pg - orc).abs().median()) < 2e-6
