@@ -35,11 +35,12 @@ __device__ __forceinline__ float act_apply_g(float v, int act, float slope) {
     }
 }
 
-// Load a (ROWS x BK) tile of an operand into smem as [BK][ROWS + 4]; mapping chosen so that the unit-stride
-// global dimension is walked by consecutive threads.
+// A (ROWS x BK) operand tile travels global -> registers (fetch_tile, issued one tile ahead so the loads overlap the
+// FMAs of the current tile) -> smem as [BK][ROWS + 4] (stash_tile); the thread mapping walks the unit-stride global
+// dimension with consecutive threads.
 template <int ROWS>
-__device__ __forceinline__ void load_tile(float (*dst)[ROWS + 4], const float* __restrict__ P, long long s_r, long long s_l,
-                                          int r0, int l0, int R, int l_end) {
+__device__ __forceinline__ void fetch_tile(float (&reg)[ROWS * BK / 256], const float* __restrict__ P, long long s_r, long long s_l,
+                                           int r0, int l0, int R, int l_end) {
     constexpr int PER = ROWS * BK / 256;
     if (s_l == 1) {
 #pragma unroll
@@ -47,7 +48,7 @@ __device__ __forceinline__ void load_tile(float (*dst)[ROWS + 4], const float* _
             const int e = threadIdx.x + q * 256;
             const int l = e % BK, r = e / BK;
             const int gr = r0 + r, gl = l0 + l;
-            dst[l][r] = (gr < R && gl < l_end) ? __ldg(P + (long long)gr * s_r + gl) : 0.f;
+            reg[q] = (gr < R && gl < l_end) ? __ldg(P + (long long)gr * s_r + gl) : 0.f;
         }
     } else {
 #pragma unroll
@@ -55,8 +56,19 @@ __device__ __forceinline__ void load_tile(float (*dst)[ROWS + 4], const float* _
             const int e = threadIdx.x + q * 256;
             const int r = e % ROWS, l = e / ROWS;
             const int gr = r0 + r, gl = l0 + l;
-            dst[l][r] = (gr < R && gl < l_end) ? __ldg(P + (long long)gr * s_r + (long long)gl * s_l) : 0.f;
+            reg[q] = (gr < R && gl < l_end) ? __ldg(P + (long long)gr * s_r + (long long)gl * s_l) : 0.f;
         }
+    }
+}
+
+template <int ROWS>
+__device__ __forceinline__ void stash_tile(float (*dst)[ROWS + 4], const float (&reg)[ROWS * BK / 256], long long s_l) {
+    constexpr int PER = ROWS * BK / 256;
+#pragma unroll
+    for (int q = 0; q < PER; ++q) {
+        const int e = threadIdx.x + q * 256;
+        if (s_l == 1) dst[e % BK][e / BK] = reg[q];
+        else dst[e / ROWS][e % ROWS] = reg[q];
     }
 }
 
@@ -76,10 +88,17 @@ __global__ void __launch_bounds__(256) sgemm_kernel(GemmArgs a) {
 #pragma unroll
         for (int v = 0; v < 4; ++v) acc[u][v] = 0.f;
     float rs[4] = {0.f, 0.f, 0.f, 0.f};
+    float ra[BM * BK / 256], rb[BN * BK / 256];
+    fetch_tile<BM>(ra, a.A, a.a_si, a.a_sl, i0, l_begin, a.M, l_end);
+    fetch_tile<BN>(rb, a.B, a.b_sj, a.b_sl, j0, l_begin, a.N, l_end);
     for (int l0 = l_begin; l0 < l_end; l0 += BK) {
-        load_tile<BM>(As, a.A, a.a_si, a.a_sl, i0, l0, a.M, l_end);
-        load_tile<BN>(Bs, a.B, a.b_sj, a.b_sl, j0, l0, a.N, l_end);
+        stash_tile<BM>(As, ra, a.a_sl);
+        stash_tile<BN>(Bs, rb, a.b_sl);
         __syncthreads();
+        if (l0 + BK < l_end) {
+            fetch_tile<BM>(ra, a.A, a.a_si, a.a_sl, i0, l0 + BK, a.M, l_end);
+            fetch_tile<BN>(rb, a.B, a.b_sj, a.b_sl, j0, l0 + BK, a.N, l_end);
+        }
 #pragma unroll
         for (int l = 0; l < BK; ++l) {
             const float4 av = *reinterpret_cast<const float4*>(&As[l][ti * 4]);
