@@ -114,27 +114,23 @@ __global__ void __launch_bounds__(256) conv_igemm_kernel(Geo g, const float* __r
 #pragma unroll
         for (int v = 0; v < RN; ++v) acc[u][v] = 0.f;
 
-    if (MODE == WGRAD) {
-        fill_ptab(l_begin, 0);
-        __syncthreads();
-    }
-    int iter = 0;
-    for (int l0 = l_begin; l0 < l_end; l0 += BK, ++iter) {
-        if (MODE != WGRAD && (iter % (LT / BK)) == 0) {
-            // decode LT reduction indices starting at l0 (the previous iteration ended with a barrier)
-            const int gl = l0 + threadIdx.x;
-            int4 e = make_int4(0, 0, 0, 0);
-            if (gl < l_end) {
-                const int ch = gl / g.KV, tap = gl - ch * g.KV;
-                const int kd = tap / g.KHW, r = tap - kd * g.KHW;
-                const int kh = r / d.KW, kw = r - kh * d.KW;
-                e.x = (MODE == FWD) ? ch * g.I + kd * g.HW + kh * d.W + kw : ch * g.O;
-                e.y = kd | (kh << 8) | (kw << 16);
-                e.z = ch * d.Cin * g.KV + tap;          // DGRAD: weight offset of (co, cin 0, tap)
-            }
-            ltab[threadIdx.x] = e;
-            __syncthreads();
+    // Operand tiles travel global -> registers (fetch, issued one iteration ahead so that the gathers overlap the FMAs
+    // of the current tile) -> shared memory (stash).
+    float ra[A_PER], rb[B_PER];
+    auto build_ltab = [&](int l0) {                      // decode LT reduction indices starting at l0
+        const int gl = l0 + threadIdx.x;
+        int4 e = make_int4(0, 0, 0, 0);
+        if (gl < l_end) {
+            const int ch = gl / g.KV, tap = gl - ch * g.KV;
+            const int kd = tap / g.KHW, r = tap - kd * g.KHW;
+            const int kh = r / d.KW, kw = r - kh * d.KW;
+            e.x = (MODE == FWD) ? ch * g.I + kd * g.HW + kh * d.W + kw : ch * g.O;
+            e.y = kd | (kh << 8) | (kw << 16);
+            e.z = ch * d.Cin * g.KV + tap;              // DGRAD: weight offset of (co, cin 0, tap)
         }
+        ltab[threadIdx.x] = e;
+    };
+    auto fetch = [&](int l0, int iter) {
         const int tl = (iter % (LT / BK)) * BK;          // offset of this iteration inside the table window
         // ---------------- A tile
         if (MODE == WGRAD) {
@@ -146,14 +142,14 @@ __global__ void __launch_bounds__(256) conv_igemm_kernel(Geo g, const float* __r
                 const int l = e % BK, r = e / BK;
                 const int i = i0 + r;
                 const int4 pe = ptab[(iter & 1) * BK + l];
-                As[l][r] = (pe.z >= 0 && i < g.Mdim) ? __ldg(wgt_or_dy + (size_t)pe.z + (size_t)i * g.O) : 0.f;
+                ra[q] = (pe.z >= 0 && i < g.Mdim) ? __ldg(wgt_or_dy + (size_t)pe.z + (size_t)i * g.O) : 0.f;
             }
         } else {
 #pragma unroll
             for (int q = 0; q < A_PER; ++q) {
                 const int e = threadIdx.x + q * 256;
                 if (TM * BK < 256 && e >= TM * BK) break;
-                const int r = e % TM, l = e / TM;       // r == threadIdx.x % TM for every q (256 % TM == 0)
+                const int l = e / TM;                   // row e % TM == threadIdx.x % TM for every q (256 % TM == 0)
                 float v = 0.f;
                 if (pvalid && l0 + l < l_end) {
                     const int4 le = ltab[tl + l];
@@ -169,7 +165,7 @@ __global__ void __launch_bounds__(256) conv_igemm_kernel(Geo g, const float* __r
                             v = __ldg(act + (p_base + le.x + od * g.OHW + oh * d.OW + ow));
                     }
                 }
-                As[l][r] = v;
+                ra[q] = v;
             }
         }
         // ---------------- B tile
@@ -180,7 +176,7 @@ __global__ void __launch_bounds__(256) conv_igemm_kernel(Geo g, const float* __r
                 if (TN * BK < 256 && e >= TN * BK) break;
                 const int l = e % BK, c = e / BK;
                 const int gl = l0 + l, j = j0 + c;
-                Bs[l][c] = (gl < l_end && j < g.Ndim) ? __ldg(wgt_or_dy + (size_t)j * g.Kdim + gl) : 0.f;
+                rb[q] = (gl < l_end && j < g.Ndim) ? __ldg(wgt_or_dy + (size_t)j * g.Kdim + gl) : 0.f;
             }
         } else if (MODE == DGRAD) {
             // B(j = cin, l = co*KV + tap) = w[(co*Cin + j)*KV + tap]
@@ -191,10 +187,8 @@ __global__ void __launch_bounds__(256) conv_igemm_kernel(Geo g, const float* __r
                 const int l = e % BK, c = e / BK;
                 const int gl = l0 + l, j = j0 + c;
                 float v = 0.f;
-                if (gl < l_end && j < g.Ndim) {
-                    v = __ldg(wgt_or_dy + (size_t)ltab[tl + l].z + (size_t)j * g.KV);
-                }
-                Bs[l][c] = v;
+                if (gl < l_end && j < g.Ndim) v = __ldg(wgt_or_dy + (size_t)ltab[tl + l].z + (size_t)j * g.KV);
+                rb[q] = v;
             }
         } else {
             // B(j = (ci, tap), l = position) = x gathered
@@ -202,7 +196,7 @@ __global__ void __launch_bounds__(256) conv_igemm_kernel(Geo g, const float* __r
             for (int q = 0; q < B_PER; ++q) {
                 const int e = threadIdx.x + q * 256;
                 if (TN * BK < 256 && e >= TN * BK) break;
-                const int c = e % TN, l = e / TN;
+                const int l = e / TN;
                 const int4 pe = ptab[(iter & 1) * BK + l];
                 float v = 0.f;
                 if (wvalid && pe.z >= 0) {
@@ -210,11 +204,44 @@ __global__ void __launch_bounds__(256) conv_igemm_kernel(Geo g, const float* __r
                     if ((unsigned)id < (unsigned)d.D && (unsigned)ih < (unsigned)d.H && (unsigned)iw < (unsigned)d.W)
                         v = __ldg(act + (pe.x + w_off));
                 }
-                Bs[l][c] = v;
+                rb[q] = v;
             }
-            fill_ptab(l0 + BK, (iter + 1) & 1);          // next iteration's positions (other buffer)
         }
+    };
+    auto stash = [&]() {
+#pragma unroll
+        for (int q = 0; q < A_PER; ++q) {
+            const int e = threadIdx.x + q * 256;
+            if (TM * BK < 256 && e >= TM * BK) break;
+            if (MODE == WGRAD) As[e % BK][e / BK] = ra[q];
+            else As[e / TM][e % TM] = ra[q];
+        }
+#pragma unroll
+        for (int q = 0; q < B_PER; ++q) {
+            const int e = threadIdx.x + q * 256;
+            if (TN * BK < 256 && e >= TN * BK) break;
+            if (MODE == WGRAD) Bs[e / TN][e % TN] = rb[q];
+            else Bs[e % BK][e / BK] = rb[q];
+        }
+    };
+
+    if (MODE == WGRAD) fill_ptab(l_begin, 0);
+    else build_ltab(l_begin);
+    __syncthreads();
+    fetch(l_begin, 0);
+    int iter = 0;
+    for (int l0 = l_begin; l0 < l_end; l0 += BK, ++iter) {
+        // WGRAD: positions of the next iteration into the other table buffer (last read two barriers ago)
+        if (MODE == WGRAD) fill_ptab(l0 + BK, (iter + 1) & 1);
+        stash();
         __syncthreads();
+        if (l0 + BK < l_end) {
+            if (MODE != WGRAD && ((iter + 1) % (LT / BK)) == 0) {
+                build_ltab(l0 + BK);                     // every fetch from the old window finished before the barrier above
+                __syncthreads();
+            }
+            fetch(l0 + BK, iter + 1);
+        }
 #pragma unroll
         for (int l = 0; l < BK; ++l) {
             float ar[RM], br[RN];

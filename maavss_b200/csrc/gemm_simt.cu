@@ -166,6 +166,17 @@ int maavss_skinny_fwd(const float*, const float*, const float*, float*, int, int
 int maavss_skinny_dgrad(const float*, const float*, float*, int, int, int, cudaStream_t);
 int maavss_skinny_wgrad(const float*, const float*, float*, float*, int, int, int, int, cudaStream_t);
 
+// Mid-size products (LSTM input projections: 512 x 1024 x 512) have ~128 output tiles, under one CTA per SM: split the
+// reduction so that >= 2 waves of CTAs are resident and accumulate with atomics into a zeroed output.
+static int auto_splits(int M, int N, int K) {
+    const int tiles = (M <= 16) ? ceil_div(N, 256) * ceil_div(M, 16) : ceil_div(N, 64) * ceil_div(M, 64);
+    if (tiles >= 296) return 1;
+    int splits = (296 + tiles - 1) / tiles;
+    const int max_splits = (K + 63) / 64;
+    if (splits > max_splits) splits = max_splits;
+    return splits < 1 ? 1 : splits;
+}
+
 extern "C" int maavss_linear_fwd(const float* x, const float* w, const float* bias, float* y, int M, int N, int K, int act,
                                  float slope, void* stream) {
     if (M == 0 || N == 0) return MAAVSS_OK;
@@ -180,7 +191,12 @@ extern "C" int maavss_linear_fwd(const float* x, const float* w, const float* bi
     a.C = y; a.c_si = N; a.c_sj = 1;
     a.M = M; a.N = N; a.K = K;
     a.bias = bias; a.act = act; a.slope = slope;
-    return launch_gemm(a, 1, (cudaStream_t)stream);
+    int splits = 1;
+    if (!bias && act == MAAVSS_ACT_NONE) {
+        splits = auto_splits(M, N, K);
+        if (splits > 1) MAAVSS_CUDA(cudaMemsetAsync(y, 0, sizeof(float) * (size_t)M * N, (cudaStream_t)stream));
+    }
+    return launch_gemm(a, splits, (cudaStream_t)stream);
 }
 
 extern "C" int maavss_linear_dgrad(const float* dz, const float* w, float* dx, int M, int N, int K, void* stream) {
@@ -198,13 +214,7 @@ extern "C" int maavss_linear_dgrad(const float* dz, const float* w, float* dx, i
     a.M = M; a.N = K; a.K = N;
     cudaStream_t st = (cudaStream_t)stream;
     // few output tiles when M is skinny: split the reduction so that >= ~2 waves of CTAs stream w
-    const int tiles = (M <= 16) ? ceil_div(K, 256) * ceil_div(M, 16) : ceil_div(K, 64) * ceil_div(M, 64);
-    int splits = 1;
-    if (tiles < 296) {
-        splits = (296 + tiles - 1) / tiles;
-        const int max_splits = (N + 63) / 64;
-        if (splits > max_splits) splits = max_splits;
-    }
+    const int splits = auto_splits(M, K, N);
     if (splits > 1) MAAVSS_CUDA(cudaMemsetAsync(dx, 0, sizeof(float) * (size_t)M * K, st));
     return launch_gemm(a, splits, st);
 }
@@ -225,5 +235,10 @@ extern "C" int maavss_linear_wgrad(const float* dz, const float* x, float* dw, f
     a.M = N; a.N = K; a.K = M;
     a.colsum = dbias;
     a.accumulate = accumulate;
-    return launch_gemm(a, 1, (cudaStream_t)stream);
+    const int splits = auto_splits(N, K, M);
+    if (splits > 1 && !accumulate) {
+        MAAVSS_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * (size_t)N * K, (cudaStream_t)stream));
+        if (dbias) MAAVSS_CUDA(cudaMemsetAsync(dbias, 0, sizeof(float) * (size_t)N, (cudaStream_t)stream));
+    }
+    return launch_gemm(a, splits, (cudaStream_t)stream);
 }
