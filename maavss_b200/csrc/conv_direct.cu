@@ -12,6 +12,7 @@
 //          stride phase matches its position (1/(SD*SH*SW) of them), weights read from a shared-memory copy.
 // Both return 1 when they handled the call and 0 when the layer is outside their envelope (caller falls back to
 // the implicit-GEMM path).
+#include <stdlib.h>
 #include "common.cuh"
 #include "../../include/maavss_b200.h"
 
@@ -146,13 +147,18 @@ __device__ __forceinline__ int div_small(int t, int S) { return S == 1 ? t : (S 
 // contributing taps only (1/(SD*SH*SW) of the kernel volume for a strided layer) with no divisibility tests.
 // Weights are staged per group of output channels as ws[co][tap][CI_T] so a tap is one LDS.128 per 4 channels.
 template <int CI_T>
-__global__ void __launch_bounds__(DG_T) dgrad_kernel(Geo g, const float* __restrict__ dy, const float* __restrict__ w,
+__global__ void __launch_bounds__(DG_T, 4) dgrad_kernel(Geo g, const float* __restrict__ dy, const float* __restrict__ w,
                                                      const float* __restrict__ bias, float* __restrict__ dx, int Q,
                                                      int co_chunk) {
     __shared__ __align__(16) float ws[DG_WS];
     const maavss_conv_desc& d = g.d;
     const int ci0 = blockIdx.y * CI_T;
-    const int q = blockIdx.x * DG_T + threadIdx.x;
+    // Threads are dealt to the CTA's 256 consecutive positions so that a warp holds positions of ONE residue mod SW: its
+    // lanes then walk the same kernel taps in lock step (the staged-weight LDS.128 is a broadcast instead of SW..KW
+    // distinct addresses) and read consecutive dy elements.
+    int tl = threadIdx.x;
+    if (d.SW > 1 && DG_T % d.SW == 0) tl = (tl % (DG_T / d.SW)) * d.SW + tl / (DG_T / d.SW);
+    const int q = blockIdx.x * DG_T + tl;
     const bool valid = q < Q;
     const int qq = valid ? q : 0;
     const int n = qq / g.I;
@@ -220,12 +226,20 @@ int maavss_conv_dgrad_direct(const maavss_conv_desc* d, const float* dy, const f
     // channels per thread: 16 when that still gives every SM a CTA, fewer for the deep 8x8 / 8x4 layers
     int CI_T = d->Cin >= 16 ? 16 : (d->Cin > 4 ? 8 : 4);
     const int sms = maavss_num_sms();
-    while (CI_T > 4 && (long long)ceil_div(Q, direct::DG_T) * ceil_div(d->Cin, CI_T) < sms) CI_T /= 2;
+    static const int cta_target = [] {                   // tuning knob (benchmarks only): MAAVSS_DGRAD_CTA_TARGET, in SMs
+        const char* e = getenv("MAAVSS_DGRAD_CTA_TARGET");
+        return e ? atoi(e) : 1;
+    }();
+    while (CI_T > 4 && (long long)ceil_div(Q, direct::DG_T) * ceil_div(d->Cin, CI_T) < (long long)cta_target * sms) CI_T /= 2;
     const int co_chunk = min(d->Cout, direct::DG_WS / (g.KV * CI_T));
     // envelope: the staged weight block must fit, and the layer must be small enough that re-reading dy per group of
     // CI_T input channels (no shared-memory reuse of dy) is cheaper than the implicit GEMM's index work
     const double fma = (double)Q * d->Cin * d->Cout * g.KV / ((double)d->SD * d->SH * d->SW);
-    if (co_chunk < 1 || Q >= (1LL << 31) || fma > 8e9 || ceil_div(d->Cin, CI_T) > 65535) return 0;
+    static const double fma_max = [] {                   // tuning knob (benchmarks only): MAAVSS_DGRAD_DIRECT_MAX_FMA
+        const char* e = getenv("MAAVSS_DGRAD_DIRECT_MAX_FMA");
+        return e ? atof(e) : 8e9;
+    }();
+    if (co_chunk < 1 || Q >= (1LL << 31) || fma > fma_max || ceil_div(d->Cin, CI_T) > 65535) return 0;
     dim3 grid(ceil_div(Q, direct::DG_T), ceil_div(d->Cin, CI_T));
     if (CI_T == 16) direct::dgrad_kernel<16><<<grid, direct::DG_T, 0, st>>>(g, dy, w, bias, dx, (int)Q, co_chunk);
     else if (CI_T == 8) direct::dgrad_kernel<8><<<grid, direct::DG_T, 0, st>>>(g, dy, w, bias, dx, (int)Q, co_chunk);
