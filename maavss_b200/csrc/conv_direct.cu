@@ -146,7 +146,7 @@ __device__ __forceinline__ int div_small(int t, int S) { return S == 1 ? t : (S 
 // box [od_min..od_max] x [oh_min..oh_max] x [ow_min..ow_max] computed once per thread, so the inner loops run over
 // contributing taps only (1/(SD*SH*SW) of the kernel volume for a strided layer) with no divisibility tests.
 // Weights are staged per group of output channels as ws[co][tap][CI_T] so a tap is one LDS.128 per 4 channels.
-template <int CI_T>
+template <int CI_T, int SW_T>   // SW_T: compile-time stride along W (0 = runtime)
 __global__ void __launch_bounds__(DG_T, 4) dgrad_kernel(Geo g, const float* __restrict__ dy, const float* __restrict__ w,
                                                      const float* __restrict__ bias, float* __restrict__ dx, int Q,
                                                      int co_chunk) {
@@ -184,18 +184,34 @@ __global__ void __launch_bounds__(DG_T, 4) dgrad_kernel(Geo g, const float* __re
         }
         __syncthreads();
         if (!valid) continue;
-        for (int col = 0; col < cc; ++col) {
-            const float* dyp = dy + ((size_t)n * d.Cout + co0 + col) * g.O;
-            const float* wp = ws + col * g.KV * CI_T;
-            for (int od = od_lo; od <= od_hi; ++od) {
-                const int kd = td - od * d.SD;
-                for (int oh = oh_lo; oh <= oh_hi; ++oh) {
-                    const int kh = th - oh * d.SH;
-                    const float* dyr = dyp + od * g.OHW + oh * d.OW;
-                    const float* wr = wp + ((kd * d.KH + kh) * d.KW + tw) * CI_T;      // + (-ow*SW)*CI_T below
-                    for (int ow = ow_lo; ow <= ow_hi; ++ow) {
-                        const float dyv = __ldg(dyr + ow);
-                        const float4* w4 = reinterpret_cast<const float4*>(wr - ow * d.SW * CI_T);
+        // (od, oh) outside, output channels inside: the row pointers advance by constants per channel and the tap loop
+        // (<= 5 contributing taps along W for the 1x9 / 5x5 stride-2 layers) is unrolled with loop-invariant predicates
+        const int wstep = (SW_T ? SW_T : d.SW) * CI_T, nw = ow_hi - ow_lo + 1;
+        for (int od = od_lo; od <= od_hi; ++od) {
+            const int kd = td - od * d.SD;
+            for (int oh = oh_lo; oh <= oh_hi; ++oh) {
+                const int kh = th - oh * d.SH;
+                const float* dyr = dy + ((size_t)n * d.Cout + co0) * g.O + od * g.OHW + oh * d.OW + ow_lo;
+                const float* wr = ws + ((kd * d.KH + kh) * d.KW + tw) * CI_T - ow_lo * wstep;
+                for (int col = 0; col < cc; ++col, dyr += g.O, wr += g.KV * CI_T) {
+#pragma unroll
+                    for (int k = 0; k < 5; ++k) {
+                        if (k < nw) {
+                            const float dyv = __ldg(dyr + k);
+                            const float4* w4 = reinterpret_cast<const float4*>(wr - k * wstep);
+#pragma unroll
+                            for (int c4 = 0; c4 < CI_T / 4; ++c4) {
+                                const float4 wv = w4[c4];
+                                acc[4 * c4 + 0] = fmaf(dyv, wv.x, acc[4 * c4 + 0]);
+                                acc[4 * c4 + 1] = fmaf(dyv, wv.y, acc[4 * c4 + 1]);
+                                acc[4 * c4 + 2] = fmaf(dyv, wv.z, acc[4 * c4 + 2]);
+                                acc[4 * c4 + 3] = fmaf(dyv, wv.w, acc[4 * c4 + 3]);
+                            }
+                        }
+                    }
+                    for (int k = 5; k < nw; ++k) {
+                        const float dyv = __ldg(dyr + k);
+                        const float4* w4 = reinterpret_cast<const float4*>(wr - k * wstep);
 #pragma unroll
                         for (int c4 = 0; c4 < CI_T / 4; ++c4) {
                             const float4 wv = w4[c4];
@@ -241,9 +257,18 @@ int maavss_conv_dgrad_direct(const maavss_conv_desc* d, const float* dy, const f
     }();
     if (co_chunk < 1 || Q >= (1LL << 31) || fma > fma_max || ceil_div(d->Cin, CI_T) > 65535) return 0;
     dim3 grid(ceil_div(Q, direct::DG_T), ceil_div(d->Cin, CI_T));
-    if (CI_T == 16) direct::dgrad_kernel<16><<<grid, direct::DG_T, 0, st>>>(g, dy, w, bias, dx, (int)Q, co_chunk);
-    else if (CI_T == 8) direct::dgrad_kernel<8><<<grid, direct::DG_T, 0, st>>>(g, dy, w, bias, dx, (int)Q, co_chunk);
-    else direct::dgrad_kernel<4><<<grid, direct::DG_T, 0, st>>>(g, dy, w, bias, dx, (int)Q, co_chunk);
+#define DG_LAUNCH(C_, S_) direct::dgrad_kernel<C_, S_><<<grid, direct::DG_T, 0, st>>>(g, dy, w, bias, dx, (int)Q, co_chunk)
+#define DG_STRIDE(C_)                        \
+    do {                                     \
+        if (d->SW == 1) DG_LAUNCH(C_, 1);    \
+        else if (d->SW == 2) DG_LAUNCH(C_, 2); \
+        else DG_LAUNCH(C_, 0);               \
+    } while (0)
+    if (CI_T == 16) DG_STRIDE(16);
+    else if (CI_T == 8) DG_STRIDE(8);
+    else DG_STRIDE(4);
+#undef DG_STRIDE
+#undef DG_LAUNCH
     MAAVSS_LAUNCH_CHECK();
     return 1;
 }
