@@ -272,3 +272,125 @@ int maavss_conv_dgrad_direct(const maavss_conv_desc* d, const float* dy, const f
     MAAVSS_LAUNCH_CHECK();
     return 1;
 }
+
+// ---------------------------------------------------------------------------------------------- FWD
+namespace direct {
+
+// y[n, co, p] = bias[co] + sum_{ci, tap} x[n, ci, p*stride - pad + tap] * w[co, ci, tap].
+// A thread owns one output position p and CO_T output channels.  Weights are staged per group of input channels as
+// ws[ci][tap][CO_T] (one LDS.128 broadcast per 4 channels and tap); x is read straight from global memory (consecutive
+// lanes read addresses SW apart, neighbouring taps hit the same lines in L1).  (kd, kh) rows run outside the channel
+// loop so that the row pointers advance by constants; the taps along W are unrolled with loop-invariant predicates.
+template <int CO_T, int KW_T>   // KW_T: compile-time kernel width (0 = runtime)
+__global__ void __launch_bounds__(DG_T, 4) fwd_kernel(Geo g, const float* __restrict__ x, const float* __restrict__ w,
+                                                      const float* __restrict__ bias, float* __restrict__ y, int P, int ci_chunk) {
+    __shared__ __align__(16) float ws[DG_WS];
+    const maavss_conv_desc& d = g.d;
+    const int KW = KW_T ? KW_T : d.KW;
+    const int co0 = blockIdx.y * CO_T;
+    const int p = blockIdx.x * DG_T + threadIdx.x;
+    const bool valid = p < P;
+    const int pp = valid ? p : 0;
+    const int n = pp / g.O;
+    const int pos = pp - n * g.O;
+    const int od = pos / g.OHW;
+    const int r = pos - od * g.OHW;
+    const int oh = r / d.OW, ow = r - oh * d.OW;
+    const int id0 = od * d.SD - d.PD, ih0 = oh * d.SH - d.PH, iw0 = ow * d.SW - d.PW;
+    const int kd_lo = max(0, -id0), kd_hi = min(d.KD - 1, d.D - 1 - id0);
+    const int kh_lo = max(0, -ih0), kh_hi = min(d.KH - 1, d.H - 1 - ih0);
+    const int kw_lo = max(0, -iw0), kw_hi = min(KW - 1, d.W - 1 - iw0);
+    float acc[CO_T];
+#pragma unroll
+    for (int c = 0; c < CO_T; ++c) acc[c] = 0.f;
+    for (int ci0 = 0; ci0 < d.Cin; ci0 += ci_chunk) {
+        const int cc = min(ci_chunk, d.Cin - ci0);
+        __syncthreads();
+        for (int e = threadIdx.x; e < cc * g.KV * CO_T; e += DG_T) {
+            const int c = e % CO_T, rr = e / CO_T;
+            const int tap = rr % g.KV, ci = rr / g.KV;
+            const int co = co0 + c;
+            ws[e] = (co < d.Cout) ? __ldg(w + ((size_t)co * d.Cin + ci0 + ci) * g.KV + tap) : 0.f;
+        }
+        __syncthreads();
+        if (!valid) continue;
+        for (int kd = kd_lo; kd <= kd_hi; ++kd) {
+            for (int kh = kh_lo; kh <= kh_hi; ++kh) {
+                const float* xr = x + ((size_t)n * d.Cin + ci0) * g.I + (size_t)(id0 + kd) * g.HW + (ih0 + kh) * d.W + iw0;
+                const float* wr = ws + ((kd * d.KH + kh) * KW) * CO_T;
+                for (int ci = 0; ci < cc; ++ci, xr += g.I, wr += g.KV * CO_T) {
+#pragma unroll
+                    for (int k = 0; k < (KW_T ? KW_T : 9); ++k) {
+                        if (k >= kw_lo && k <= kw_hi) {
+                            const float xv = __ldg(xr + k);
+                            const float4* w4 = reinterpret_cast<const float4*>(wr + k * CO_T);
+#pragma unroll
+                            for (int c4 = 0; c4 < CO_T / 4; ++c4) {
+                                const float4 wv = w4[c4];
+                                acc[4 * c4 + 0] = fmaf(xv, wv.x, acc[4 * c4 + 0]);
+                                acc[4 * c4 + 1] = fmaf(xv, wv.y, acc[4 * c4 + 1]);
+                                acc[4 * c4 + 2] = fmaf(xv, wv.z, acc[4 * c4 + 2]);
+                                acc[4 * c4 + 3] = fmaf(xv, wv.w, acc[4 * c4 + 3]);
+                            }
+                        }
+                    }
+                    if (!KW_T) {
+                        for (int k = max(9, kw_lo); k <= kw_hi; ++k) {
+                            const float xv = __ldg(xr + k);
+                            const float4* w4 = reinterpret_cast<const float4*>(wr + k * CO_T);
+#pragma unroll
+                            for (int c4 = 0; c4 < CO_T / 4; ++c4) {
+                                const float4 wv = w4[c4];
+                                acc[4 * c4 + 0] = fmaf(xv, wv.x, acc[4 * c4 + 0]);
+                                acc[4 * c4 + 1] = fmaf(xv, wv.y, acc[4 * c4 + 1]);
+                                acc[4 * c4 + 2] = fmaf(xv, wv.z, acc[4 * c4 + 2]);
+                                acc[4 * c4 + 3] = fmaf(xv, wv.w, acc[4 * c4 + 3]);
+                            }
+                        }
+                    }
+                }
+            }
+        }
+    }
+    if (!valid) return;
+#pragma unroll
+    for (int c = 0; c < CO_T; ++c) {
+        const int co = co0 + c;
+        if (co < d.Cout) y[((size_t)n * d.Cout + co) * g.O + pos] = acc[c] + (bias ? __ldg(bias + co) : 0.f);
+    }
+}
+
+}  // namespace direct
+
+int maavss_conv_fwd_direct(const maavss_conv_desc* d, const float* x, const float* w, const float* bias, float* y, cudaStream_t st) {
+    direct::Geo g = direct::make_geo(d);
+    const long long P = (long long)d->N * g.O;
+    int CO_T = d->Cout >= 16 ? 16 : (d->Cout > 4 ? 8 : 4);
+    const int sms = maavss_num_sms();
+    while (CO_T > 4 && (long long)ceil_div(P, direct::DG_T) * ceil_div(d->Cout, CO_T) < sms) CO_T /= 2;
+    const int ci_chunk = min(d->Cin, direct::DG_WS / (g.KV * CO_T));
+    // envelope (bench.py --breakdown on B200, profiles/r1_step_breakdown_*.txt): layers up to 5e8 FMAs with >= 4096
+    // output positions run 5-40 % faster here (thin layers 1.5-2x); the implicit GEMM's shared-memory reuse of x wins
+    // beyond that and for the 8x4 / 8x8 maps whose 2048 positions leave most SMs without a CTA
+    const double fma = (double)P * d->Cin * d->Cout * g.KV;
+    static const double fma_max = [] {                   // tuning knob (benchmarks only): MAAVSS_FWD_DIRECT_MAX_FMA
+        const char* e = getenv("MAAVSS_FWD_DIRECT_MAX_FMA");
+        return e ? atof(e) : 5e8;
+    }();
+    if (ci_chunk < 1 || P >= (1LL << 31) || P < 4096 || fma > fma_max || ceil_div(d->Cout, CO_T) > 65535) return 0;
+    dim3 grid(ceil_div(P, direct::DG_T), ceil_div(d->Cout, CO_T));
+#define FW_LAUNCH(C_, K_) direct::fwd_kernel<C_, K_><<<grid, direct::DG_T, 0, st>>>(g, x, w, bias, y, (int)P, ci_chunk)
+#define FW_WIDTH(C_)                           \
+    do {                                       \
+        if (d->KW == 9) FW_LAUNCH(C_, 9);      \
+        else if (d->KW == 5) FW_LAUNCH(C_, 5); \
+        else FW_LAUNCH(C_, 0);                 \
+    } while (0)
+    if (CO_T == 16) FW_WIDTH(16);
+    else if (CO_T == 8) FW_WIDTH(8);
+    else FW_WIDTH(4);
+#undef FW_WIDTH
+#undef FW_LAUNCH
+    MAAVSS_LAUNCH_CHECK();
+    return 1;
+}

@@ -384,12 +384,15 @@ int launch(igemm::Geo g, const float* a, const float* b, const float* bias, floa
 
 int maavss_conv_wgrad_direct(const maavss_conv_desc*, const float*, const float*, float*, int, cudaStream_t);
 int maavss_conv_dgrad_direct(const maavss_conv_desc*, const float*, const float*, const float*, float*, cudaStream_t);
+int maavss_conv_fwd_direct(const maavss_conv_desc*, const float*, const float*, const float*, float*, cudaStream_t);
 
 extern "C" int maavss_conv_fwd(const maavss_conv_desc* d, const float* x, const float* w, const float* bias, float* y, void* stream) {
     int rc = check_desc(d, "conv_fwd");
     if (rc) return rc;
     if (d->N == 0) return MAAVSS_OK;
     MAAVSS_CHECK_ARG(x && w && y, "conv_fwd: null argument");
+    rc = maavss_conv_fwd_direct(d, x, w, bias, y, (cudaStream_t)stream);
+    if (rc != 0) return rc < 0 ? rc : MAAVSS_OK;
     igemm::Geo g = make_geo(d);
     g.Mdim = d->N * g.O;
     g.Ndim = d->Cout;
