@@ -98,7 +98,6 @@ class AV_Fusion_Model(nn.Module):
 
     # ---- avse_model.py:680-711 ----
     def forward(self, x_a, x_v):
-        x_a_enc = self.stft_encoder(x_a)
-        x_v_enc = self.phasegram_encoder(x_v)
+        x_a_enc, x_v_enc = L.run_pair(self.stft_encoder, x_a, self.phasegram_encoder, x_v)
         fused = self.av_fusion_forward(x_a_enc, x_v_enc)
         return self.a_fc1(fused).view(x_a.shape), self.v_fc1(fused).view(x_v.shape), fused

@@ -14,8 +14,7 @@ class AV_Fusion_Model(_Base):
 
     # ---- avse_model_conv.py:700-719 ----
     def forward(self, x_a, x_v):
-        x_a_enc = self.stft_encoder(x_a)
-        x_v_enc = self.phasegram_encoder(x_v)
+        x_a_enc, x_v_enc = L.run_pair(self.stft_encoder, x_a, self.phasegram_encoder, x_v)
         fused = self.av_fusion_forward(x_a_enc, x_v_enc)
         x_a_out = self.stft_decoder(fused.view(x_a_enc.shape))
         x_v_out = self.phasegram_decoder(fused.view(x_v_enc.shape))

@@ -69,8 +69,7 @@ class AV_Fusion_Model_Frames(nn.Module):
 
     # ---- avse_model_final.py:258-274 ----
     def forward(self, x_a, x_v):
-        x_a_enc = self.stft_encoder(x_a)
-        x_v_enc = self.visual_encoder(x_v)
+        x_a_enc, x_v_enc = L.run_pair(self.stft_encoder, x_a, self.visual_encoder, x_v)
         fused = self.av_fusion_forward(x_a_enc, x_v_enc)
         a = self.a_fc1[0].fused_forward(fused, ops.ACT_TANH)
         v = self.v_fc1[0].fused_forward(fused, ops.ACT_SIGMOID)

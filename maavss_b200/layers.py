@@ -125,7 +125,8 @@ _ACTS = (Tanh, Sigmoid, LeakyReLU)
 class FusedSequential(nn.Sequential):
     """nn.Sequential that runs (BatchNorm, activation) and (Linear, activation) pairs as one fused op."""
 
-    def forward(self, x):
+    def steps(self, x):
+        """Generator over the fused ops: yields the running activation after each one (run_pair interleaves two of these)."""
         mods = list(self)
         i = 0
         while i < len(mods):
@@ -138,4 +139,51 @@ class FusedSequential(nn.Sequential):
             else:
                 x = m(x)
                 i += 1
+            yield x
+
+    def forward(self, x):
+        for x in self.steps(x):
+            pass
         return x
+
+
+# The audio and the video encoder of the fusion models are independent until the LSTM (avse_model.py:680-690) and their
+# layers are small (128-512 CTAs): run_pair() issues them on two streams, one layer of each in turn, so that the kernels
+# of one branch fill the SMs the other leaves idle and (data parallel) the sync-BatchNorm collectives of one branch hide
+# behind the other's convolutions.  Autograd replays each op's backward on its forward stream, so the backward overlaps
+# the same way.  The fork / join are event waits: they are captured into the train step's CUDA graph like any launch.
+PARALLEL_BRANCHES = True
+_side_streams = {}
+
+
+def _side_stream(device):
+    s = _side_streams.get(device)
+    if s is None:
+        s = _side_streams[device] = torch.cuda.Stream(device=device)
+    return s
+
+
+def run_pair(seq_main, x_main, seq_side, x_side):
+    """(seq_main(x_main), seq_side(x_side)) with the two FusedSequentials interleaved on the current and a side stream."""
+    if not (PARALLEL_BRANCHES and x_main.is_cuda and x_side.is_cuda):
+        return seq_main(x_main), seq_side(x_side)
+    cur = torch.cuda.current_stream(x_main.device)
+    side = _side_stream(x_main.device)
+    side.wait_stream(cur)
+    ga, gb = seq_main.steps(x_main), seq_side.steps(x_side)
+    a, b, done_a, done_b = x_main, x_side, False, False
+    while not (done_a and done_b):
+        if not done_b:
+            with torch.cuda.stream(side):
+                try:
+                    b = next(gb)
+                except StopIteration:
+                    done_b = True
+        if not done_a:
+            try:
+                a = next(ga)
+            except StopIteration:
+                done_a = True
+    cur.wait_stream(side)
+    b.record_stream(cur)
+    return a, b
