@@ -377,7 +377,9 @@ int maavss_conv_fwd_direct(const maavss_conv_desc* d, const float* x, const floa
         const char* e = getenv("MAAVSS_FWD_DIRECT_MAX_FMA");
         return e ? atof(e) : 5e8;
     }();
-    if (ci_chunk < 1 || P >= (1LL << 31) || P < 4096 || fma > fma_max || ceil_div(d->Cout, CO_T) > 65535) return 0;
+    // (a single group of output channels reads x exactly once: any size, e.g. the C1->16 first Conv3d of the Frames model)
+    const bool single_group = ceil_div(d->Cout, CO_T) == 1 && d->Cin <= 4;
+    if (ci_chunk < 1 || P >= (1LL << 31) || P < 4096 || (fma > fma_max && !single_group) || ceil_div(d->Cout, CO_T) > 65535) return 0;
     dim3 grid(ceil_div(P, direct::DG_T), ceil_div(d->Cout, CO_T));
 #define FW_LAUNCH(C_, K_) direct::fwd_kernel<C_, K_><<<grid, direct::DG_T, 0, st>>>(g, x, w, bias, y, (int)P, ci_chunk)
 #define FW_WIDTH(C_)                           \

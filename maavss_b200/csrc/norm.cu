@@ -2,6 +2,7 @@
 // (nn.BatchNorm2d + nn.Tanh, avse_model.py:440-441,498-499; avse_model_final.py:103-104).
 // HBM-bound: x is read once for the statistics and once for the apply; the statistics are split in two halves
 // so that a data-parallel caller can all-reduce the per-channel partial sums in between.
+#include <stdint.h>
 #include "common.cuh"
 #include "../../include/maavss_b200.h"
 
@@ -168,20 +169,52 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(const float* _
 // change between them).  Launch 1 = partial sums per (group, channel, split); launch 2 = apply, every CTA re-deriving
 // its (group, channel) statistics from the few partials (no separate finalize launch); one designated CTA per
 // channel publishes stats and applies the G running-statistics updates in window order.
+// Walks this CTA's chunk of the flattened (n, i) index space of one (group, channel) in units of V floats, calling
+// f(element offset).  One division per thread; afterwards (n, i) advance by the constant (q, r) = divmod(256, inner / V).
+template <int V, class F>
+__device__ __forceinline__ void bn_walk(int Ng, long long inner, size_t row0, int C, F&& f) {
+    const long long innerV = inner / V, total = (long long)Ng * innerV;
+    const long long chunk = (total + gridDim.x - 1) / gridDim.x;
+    const long long e0 = (long long)blockIdx.x * chunk, e1 = min(total, e0 + chunk);
+    long long e = e0 + threadIdx.x;
+    if (e >= e1) return;
+    long long n = e / innerV, i = e - n * innerV;
+    const long long q = kBnThreads / innerV, r = kBnThreads - q * innerV;
+    for (; e < e1; e += kBnThreads) {
+        f((row0 + (size_t)n * C) * (size_t)inner + (size_t)i * V);
+        i += r;
+        n += q;
+        if (i >= innerV) {
+            i -= innerV;
+            ++n;
+        }
+    }
+}
+
+__device__ __forceinline__ bool bn_vec_ok(long long inner, const void* a, const void* b, const void* c) {
+    return (inner & 3) == 0 && ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(c)) & 15) == 0;
+}
+
 __global__ void __launch_bounds__(kBnThreads) bn_reduce_g_kernel(const float* __restrict__ x, int Ng, int C, long long inner,
                                                                  double* __restrict__ partial) {
     const int c = blockIdx.y, S = gridDim.x, g = blockIdx.z;
-    const long long total = (long long)Ng * inner;
-    const long long chunk = (total + S - 1) / S;
-    const long long e0 = (long long)blockIdx.x * chunk, e1 = min(total, e0 + chunk);
-    float s1 = 0.f, s2 = 0.f;
-    for (long long e = e0 + threadIdx.x; e < e1; e += kBnThreads) {
-        const long long n = e / inner, i = e - n * inner;
-        const float v = x[((size_t)(g * Ng + n) * C + c) * inner + i];
-        s1 += v;
-        s2 = fmaf(v, v, s2);
+    const size_t row0 = (size_t)g * Ng * C + c;
+    float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+    if (bn_vec_ok(inner, x, x, x)) {
+        bn_walk<4>(Ng, inner, row0, C, [&](size_t off) {
+            const float4 v = *reinterpret_cast<const float4*>(x + off);
+            s1[0] += v.x; s1[1] += v.y; s1[2] += v.z; s1[3] += v.w;
+            s2[0] = fmaf(v.x, v.x, s2[0]); s2[1] = fmaf(v.y, v.y, s2[1]); s2[2] = fmaf(v.z, v.z, s2[2]); s2[3] = fmaf(v.w, v.w, s2[3]);
+        });
+    } else {
+        bn_walk<1>(Ng, inner, row0, C, [&](size_t off) {
+            const float v = x[off];
+            s1[0] += v;
+            s2[0] = fmaf(v, v, s2[0]);
+        });
     }
-    block_sum2((double)s1, (double)s2, partial + (((size_t)g * C + c) * S + blockIdx.x) * 2);
+    block_sum2(((double)s1[0] + (double)s1[1]) + ((double)s1[2] + (double)s1[3]),
+               ((double)s2[0] + (double)s2[1]) + ((double)s2[2] + (double)s2[3]), partial + (((size_t)g * C + c) * S + blockIdx.x) * 2);
 }
 
 __device__ __forceinline__ void stats_from_partial(const double* __restrict__ partial, int S, double count, float eps,
@@ -246,18 +279,29 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_g_kernel(const float
                                                                      double* __restrict__ partial) {
     const int c = blockIdx.y, S = gridDim.x, g = blockIdx.z;
     const float mean = stats[((size_t)g * C + c) * 2], invstd = stats[((size_t)g * C + c) * 2 + 1];
-    const long long total = (long long)Ng * inner;
-    const long long chunk = (total + S - 1) / S;
-    const long long e0 = (long long)blockIdx.x * chunk, e1 = min(total, e0 + chunk);
-    float s1 = 0.f, s2 = 0.f;
-    for (long long e = e0 + threadIdx.x; e < e1; e += kBnThreads) {
-        const long long n = e / inner, i = e - n * inner;
-        const size_t q = ((size_t)(g * Ng + n) * C + c) * inner + i;
-        const float dz = dy[q] * act_grad(y[q], act, slope);
-        s1 += dz;
-        s2 = fmaf(dz, (x[q] - mean) * invstd, s2);
+    const size_t row0 = (size_t)g * Ng * C + c;
+    float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+    if (bn_vec_ok(inner, dy, y, x)) {
+        bn_walk<4>(Ng, inner, row0, C, [&](size_t off) {
+            const float4 d4 = *reinterpret_cast<const float4*>(dy + off), y4 = *reinterpret_cast<const float4*>(y + off),
+                         x4 = *reinterpret_cast<const float4*>(x + off);
+            const float dv[4] = {d4.x, d4.y, d4.z, d4.w}, yv[4] = {y4.x, y4.y, y4.z, y4.w}, xv[4] = {x4.x, x4.y, x4.z, x4.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float dz = dv[k] * act_grad(yv[k], act, slope);
+                s1[k] += dz;
+                s2[k] = fmaf(dz, (xv[k] - mean) * invstd, s2[k]);
+            }
+        });
+    } else {
+        bn_walk<1>(Ng, inner, row0, C, [&](size_t off) {
+            const float dz = dy[off] * act_grad(y[off], act, slope);
+            s1[0] += dz;
+            s2[0] = fmaf(dz, (x[off] - mean) * invstd, s2[0]);
+        });
     }
-    block_sum2((double)s1, (double)s2, partial + (((size_t)g * C + c) * S + blockIdx.x) * 2);
+    block_sum2(((double)s1[0] + (double)s1[1]) + ((double)s1[2] + (double)s1[3]),
+               ((double)s2[0] + (double)s2[1]) + ((double)s2[2] + (double)s2[3]), partial + (((size_t)g * C + c) * S + blockIdx.x) * 2);
 }
 
 __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_fused_kernel(const float* __restrict__ dy, const float* __restrict__ y,
