@@ -11,14 +11,14 @@
 
 namespace tcg {
 
-constexpr int BM = 128, BK = 64, ACC_STAGES = 2, THREADS = 192;
+constexpr int BM = 128, BK = 64, ACC_STAGES = 2, EPI_WARPS = 8, THREADS = 64 + 32 * EPI_WARPS;
 
 template <int BN>
 struct Smem {
     static constexpr int STAGES = BN > 128 ? 4 : 5;
     static constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int EPI_BYTES = 4 * 32 * 32 * 4;
+    static constexpr int EPI_BYTES = EPI_WARPS * 32 * 32 * 4;
     static constexpr int BAR_OFF = STAGES * STAGE_BYTES + EPI_BYTES;
     static constexpr int TOTAL = BAR_OFF + 256 + 1024;    // barriers + tmem slot, + slack for the 1024-byte alignment
 };
@@ -33,7 +33,25 @@ struct Epilogue {
     int act;                 // MAAVSS_ACT_NONE or MAAVSS_ACT_GELU
 };
 
-__device__ __forceinline__ float gelu_erf(float v) { return 0.5f * v * (1.f + erff(v * 0.70710678118654752f)); }
+// erf by Abramowitz & Stegun 7.1.26 (|error| <= 1.5e-7, the size of erff's own rounding): one MUFU.RCP, one MUFU.EX2 and
+// 8 FMA-class instructions instead of erff's ~45 -- the fc1 epilogue was bound by erff on its few epilogue warps
+// (ncu: 322 us for fc1 + GELU against 103 us for fc2 with the same FLOPs).
+__device__ __forceinline__ float rcp_approx(float x) {   // MUFU.RCP (1 ulp); __frcp_rn is the IEEE routine with a CALL slow path
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float erf_as(float x) {
+    const float ax = fabsf(x);
+    const float t = rcp_approx(fmaf(0.3275911f, ax, 1.f));
+    float p = fmaf(t, 1.061405429f, -1.453152027f);
+    p = fmaf(t, p, 1.421413741f);
+    p = fmaf(t, p, -0.284496736f);
+    p = fmaf(t, p, 0.254829592f);
+    const float r = fmaf(-p * t, __expf(-ax * ax), 1.f);
+    return copysignf(r, x);
+}
+__device__ __forceinline__ float gelu_erf(float v) { return 0.5f * v * (1.f + erf_as(v * 0.70710678118654752f)); }
 
 template <int BN>
 __global__ void __launch_bounds__(THREADS, 1) tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA,
@@ -65,7 +83,7 @@ __global__ void __launch_bounds__(THREADS, 1) tc_gemm_kernel(const __grid_consta
         }
         for (int a = 0; a < ACC_STAGES; ++a) {
             tc::mbar_init(&tfull[a], 1);
-            tc::mbar_init(&tempty[a], 4);
+            tc::mbar_init(&tempty[a], EPI_WARPS);
         }
         tc::fence_barrier_init();
     }
@@ -118,9 +136,13 @@ __global__ void __launch_bounds__(THREADS, 1) tc_gemm_kernel(const __grid_consta
             }
         }
     } else {
-        const int q = warp & 3;                      // TMEM lane quadrant this warp may access
-        float* stage = epi + q * (32 * 32);          // 32 rows x 32 fp32, 16-byte chunks XOR-swizzled by (row & 7)
+        // 8 epilogue warps: warp w may access TMEM lanes 32 * (w % 4) .. + 31, so two warps share each lane quadrant and
+        // take alternate 32-column chunks; the tcgen05.ld of a warp's next chunk is in flight while it transposes,
+        // finishes and stores the current one.
+        const int ew = warp - 2, q = warp & 3, half = ew >> 2;
+        float* stage = epi + ew * (32 * 32);         // 32 rows x 32 fp32, 16-byte chunks XOR-swizzled by (row & 7)
         const int sub = lane >> 3, cc = (lane & 7) * 4;     // phase 2: 4 rows per pass, 8 lanes x float4 per row
+        constexpr int CH = (BN / 32 + 1) / 2;        // chunks per warp (the second half gets one fewer when BN / 32 is odd)
         int it = 0;
         for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++it) {
             const int m0 = (t / n_tiles) * BM, n0 = (t % n_tiles) * BN;
@@ -128,11 +150,16 @@ __global__ void __launch_bounds__(THREADS, 1) tc_gemm_kernel(const __grid_consta
             const uint32_t aph = (it >> 1) & 1;
             tc::mbar_wait(&tfull[a], aph);
             tc::tc_fence_after();
-#pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
-                uint32_t r[32];
-                tc::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + a * BN + c * 32, r);
+            const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + a * BN;
+            uint32_t rbuf[2][32];
+            if (half * 32 < BN) tc::tmem_ld_32x32(t_addr + half * 32, rbuf[0]);
+#pragma unroll
+            for (int i = 0; i < CH; ++i) {
+                const int c = half + 2 * i;
+                if (c * 32 >= BN) break;
+                uint32_t (&r)[32] = rbuf[i & 1];
                 tc::tmem_ld_wait();
+                if ((c + 2) * 32 < BN) tc::tmem_ld_32x32(t_addr + (c + 2) * 32, rbuf[(i + 1) & 1]);
 #pragma unroll
                 for (int j = 0; j < 8; ++j)
                     *reinterpret_cast<uint4*>(&stage[lane * 32 + ((j ^ (lane & 7)) << 2)]) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
