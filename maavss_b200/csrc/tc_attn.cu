@@ -14,6 +14,14 @@
 
 namespace tca {
 
+// MUFU.EX2 directly: the arguments are <= 0 (score minus row maximum), exp2f()'s range scaling is not needed
+__device__ __forceinline__ float ex2_approx(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+
 constexpr int BQ = 128, BKV = 128, HD = 64, KSTAGES = 3, VSTAGES = 2, THREADS = 320;   // 2 + 8 softmax warps
 constexpr int TILE_BYTES = 128 * HD * 2;                 // 16 KB: 128 tokens x 64 dims bf16
 constexpr int P_BYTES = 2 * TILE_BYTES;                  // 128 x 128 bf16 as two K-major halves of 64 kv
@@ -172,24 +180,41 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_kernel(const __grid_const
             const int valid = N - j * BKV;
             // this warp's 64 kv columns are the K-major half `hf` of the P tile: one 128-byte row per query
             uint8_t* prow = smem + OFF_P + hf * TILE_BYTES + row * 128;
+            // both 32-column chunks are requested up front: the second tcgen05.ld is in flight while the first is turned
+            // into probabilities.  Only the last kv tile has columns beyond the sequence: the mask lives in its own
+            // (warp-uniform) branch instead of costing a compare + select per element everywhere.
+            uint32_t rr[2][32];
+            tc::tmem_ld_32x32(tmem + lane_off + b * BKV + (hf * 2) * 32, rr[0]);
+            tc::tmem_ld_32x32(tmem + lane_off + b * BKV + (hf * 2 + 1) * 32, rr[1]);
+            tc::tmem_ld_wait();
+            float l0 = 0.f, l1 = 0.f;
 #pragma unroll
             for (int c2 = 0; c2 < 2; ++c2) {
                 const int c = hf * 2 + c2;
-                uint32_t r[32];
-                tc::tmem_ld_32x32(tmem + lane_off + b * BKV + c * 32, r);
-                tc::tmem_ld_wait();
+                const uint32_t (&r)[32] = rr[c2];
                 uint32_t packed[16];
+                if (valid >= BKV) {
 #pragma unroll
-                for (int i = 0; i < 32; i += 2) {
-                    float p0 = exp2f(fmaf(__uint_as_float(r[i]), scale_log2e, -mb));
-                    float p1 = exp2f(fmaf(__uint_as_float(r[i + 1]), scale_log2e, -mb));
-                    if (valid < BKV) {
+                    for (int i = 0; i < 32; i += 2) {
+                        const float p0 = ex2_approx(fmaf(__uint_as_float(r[i]), scale_log2e, -mb));
+                        const float p1 = ex2_approx(fmaf(__uint_as_float(r[i + 1]), scale_log2e, -mb));
+                        l0 += p0;
+                        l1 += p1;
+                        const __nv_bfloat162 pk = __floats2bfloat162_rn(p0, p1);
+                        packed[i >> 1] = *reinterpret_cast<const uint32_t*>(&pk);
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; i += 2) {
+                        float p0 = ex2_approx(fmaf(__uint_as_float(r[i]), scale_log2e, -mb));
+                        float p1 = ex2_approx(fmaf(__uint_as_float(r[i + 1]), scale_log2e, -mb));
                         if (c * 32 + i >= valid) p0 = 0.f;
                         if (c * 32 + i + 1 >= valid) p1 = 0.f;
+                        l0 += p0;
+                        l1 += p1;
+                        const __nv_bfloat162 pk = __floats2bfloat162_rn(p0, p1);
+                        packed[i >> 1] = *reinterpret_cast<const uint32_t*>(&pk);
                     }
-                    l += p0 + p1;
-                    const __nv_bfloat162 pk = __floats2bfloat162_rn(p0, p1);
-                    packed[i >> 1] = *reinterpret_cast<const uint32_t*>(&pk);
                 }
 #pragma unroll
                 for (int ch = 0; ch < 4; ++ch) {
@@ -198,6 +223,7 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_kernel(const __grid_const
                         make_uint4(packed[ch * 4], packed[ch * 4 + 1], packed[ch * 4 + 2], packed[ch * 4 + 3]);
                 }
             }
+            l += l0 + l1;
             tc::tc_fence_before();
             tc::fence_proxy_async();          // generic-proxy smem writes -> visible to the tensor core (async proxy)
             __syncwarp();
