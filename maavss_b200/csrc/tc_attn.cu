@@ -26,7 +26,7 @@ constexpr int BQ = 128, BKV = 128, HD = 64, KSTAGES = 3, VSTAGES = 2, THREADS = 
 constexpr int TILE_BYTES = 128 * HD * 2;                 // 16 KB: 128 tokens x 64 dims bf16
 constexpr int P_BYTES = 2 * TILE_BYTES;                  // 128 x 128 bf16 as two K-major halves of 64 kv
 constexpr int OFF_Q = 0, OFF_K = TILE_BYTES, OFF_V = OFF_K + KSTAGES * TILE_BYTES, OFF_P = OFF_V + VSTAGES * TILE_BYTES;
-constexpr int OFF_BAR = OFF_P + P_BYTES;
+constexpr int OFF_BAR = OFF_P + 2 * P_BYTES;       // P is double-buffered: softmax(j+1) overlaps the P V product of tile j
 constexpr int OFF_XCH = OFF_BAR + 256;                   // 2 x 128 floats: row max / row sum exchange between column halves
 constexpr int SMEM_TOTAL = OFF_XCH + 1024 + 1024;
 constexpr int TMEM_COLS = 512;                           // S0 [0,128) S1 [128,256) O [256,320)
@@ -43,9 +43,9 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_kernel(const __grid_const
     uint64_t* v_empty = v_full + VSTAGES;
     uint64_t* s_full = v_empty + VSTAGES;   // 2
     uint64_t* s_empty = s_full + 2;         // 2
-    uint64_t* p_full = s_empty + 2;         // 1
-    uint64_t* p_empty = p_full + 1;         // 1
-    uint64_t* o_full = p_empty + 1;         // 1
+    uint64_t* p_full = s_empty + 2;         // 2
+    uint64_t* p_empty = p_full + 2;         // 2
+    uint64_t* o_full = p_empty + 2;         // 1
     uint32_t* tmem_slot = (uint32_t*)(o_full + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -59,8 +59,7 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_kernel(const __grid_const
         for (int s = 0; s < KSTAGES; ++s) { tc::mbar_init(&k_full[s], 1); tc::mbar_init(&k_empty[s], 1); }
         for (int s = 0; s < VSTAGES; ++s) { tc::mbar_init(&v_full[s], 1); tc::mbar_init(&v_empty[s], 1); }
         for (int b = 0; b < 2; ++b) { tc::mbar_init(&s_full[b], 1); tc::mbar_init(&s_empty[b], 8); }
-        tc::mbar_init(p_full, 8);
-        tc::mbar_init(p_empty, 1);
+        for (int b = 0; b < 2; ++b) { tc::mbar_init(&p_full[b], 8); tc::mbar_init(&p_empty[b], 1); }
         tc::mbar_init(o_full, 1);
         tc::fence_barrier_init();
     }
@@ -114,10 +113,10 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_kernel(const __grid_const
             issue_s(nkv);                                                  // pass 2, software-pipelined by one tile
             for (int j = 0; j < nkv; ++j) {
                 if (j + 1 < nkv) issue_s(nkv + j + 1);
-                tc::mbar_wait(p_full, j & 1);
+                tc::mbar_wait(&p_full[j & 1], (j >> 1) & 1);
                 tc::mbar_wait(&v_full[vs], vph);
                 tc::tc_fence_after();
-                const uint32_t p_addr = tc::smem_u32(smem + OFF_P);
+                const uint32_t p_addr = tc::smem_u32(smem + OFF_P + (j & 1) * P_BYTES);
                 const uint32_t v_addr = tc::smem_u32(smem + OFF_V + vs * TILE_BYTES);
 #pragma unroll
                 for (int k = 0; k < BKV / 16; ++k) {
@@ -127,7 +126,7 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_kernel(const __grid_const
                     const uint64_t vdesc = tc::smem_desc_k_sw128(v_addr + k * 2048);
                     tc::umma_f16(tmem + 2 * BKV, pdesc, vdesc, idesc_o, (j | k) != 0);
                 }
-                tc::umma_commit(p_empty);
+                tc::umma_commit(&p_empty[j & 1]);
                 tc::umma_commit(&v_empty[vs]);
                 if (++vs == VSTAGES) { vs = 0; vph ^= 1; }
             }
@@ -175,11 +174,10 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_kernel(const __grid_const
         for (int j = 0; j < nkv; ++j) {
             const int g = nkv + j, b = g & 1;
             tc::mbar_wait(&s_full[b], (g >> 1) & 1);
-            tc::mbar_wait(p_empty, (j & 1) ^ 1);
             tc::tc_fence_after();
             const int valid = N - j * BKV;
             // this warp's 64 kv columns are the K-major half `hf` of the P tile: one 128-byte row per query
-            uint8_t* prow = smem + OFF_P + hf * TILE_BYTES + row * 128;
+            uint8_t* prow = smem + OFF_P + (j & 1) * P_BYTES + hf * TILE_BYTES + row * 128;
             // both 32-column chunks are requested up front: the second tcgen05.ld is in flight while the first is turned
             // into probabilities.  Only the last kv tile has columns beyond the sequence: the mask lives in its own
             // (warp-uniform) branch instead of costing a compare + select per element everywhere.
@@ -188,11 +186,12 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_kernel(const __grid_const
             tc::tmem_ld_32x32(tmem + lane_off + b * BKV + (hf * 2 + 1) * 32, rr[1]);
             tc::tmem_ld_wait();
             float l0 = 0.f, l1 = 0.f;
+            uint32_t pk[2][16];
 #pragma unroll
             for (int c2 = 0; c2 < 2; ++c2) {
                 const int c = hf * 2 + c2;
                 const uint32_t (&r)[32] = rr[c2];
-                uint32_t packed[16];
+                uint32_t (&packed)[16] = pk[c2];
                 if (valid >= BKV) {
 #pragma unroll
                     for (int i = 0; i < 32; i += 2) {
@@ -200,8 +199,8 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_kernel(const __grid_const
                         const float p1 = ex2_approx(fmaf(__uint_as_float(r[i + 1]), scale_log2e, -mb));
                         l0 += p0;
                         l1 += p1;
-                        const __nv_bfloat162 pk = __floats2bfloat162_rn(p0, p1);
-                        packed[i >> 1] = *reinterpret_cast<const uint32_t*>(&pk);
+                        const __nv_bfloat162 pb = __floats2bfloat162_rn(p0, p1);
+                        packed[i >> 1] = *reinterpret_cast<const uint32_t*>(&pb);
                     }
                 } else {
 #pragma unroll
@@ -212,10 +211,15 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_kernel(const __grid_const
                         if (c * 32 + i + 1 >= valid) p1 = 0.f;
                         l0 += p0;
                         l1 += p1;
-                        const __nv_bfloat162 pk = __floats2bfloat162_rn(p0, p1);
-                        packed[i >> 1] = *reinterpret_cast<const uint32_t*>(&pk);
+                        const __nv_bfloat162 pb = __floats2bfloat162_rn(p0, p1);
+                        packed[i >> 1] = *reinterpret_cast<const uint32_t*>(&pb);
                     }
                 }
+            }
+            tc::mbar_wait(&p_empty[j & 1], ((j >> 1) & 1) ^ 1);      // the P V product that last read this P buffer (tile j - 2)
+#pragma unroll
+            for (int c2 = 0; c2 < 2; ++c2) {
+                const uint32_t (&packed)[16] = pk[c2];
 #pragma unroll
                 for (int ch = 0; ch < 4; ++ch) {
                     const int chunk = c2 * 4 + ch;
@@ -229,7 +233,7 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_kernel(const __grid_const
             __syncwarp();
             if (lane == 0) {
                 tc::mbar_arrive(&s_empty[b]);
-                tc::mbar_arrive(p_full);
+                tc::mbar_arrive(&p_full[j & 1]);
             }
         }
         asm volatile("bar.sync 1, 256;" ::: "memory");        // both halves are done reading the maxima
