@@ -12,7 +12,7 @@ no per-op Python on the replay path.  `graph=False` runs the same code eagerly (
 """
 import torch
 
-from . import nn_ops, parallel, phasegram_ops
+from . import layers, nn_ops, parallel, phasegram_ops
 
 
 class _TrainStepBase:
@@ -112,8 +112,19 @@ class FusionTrainStep(_TrainStepBase):
     def _windows_batched(self, x_stft, y_stft, attn):
         G, B = self.num_seq, x_stft.shape[0]
         span = self.hpf * self.num_frames
-        pgram = torch.cat([phasegram_ops.video_phasegram(attn[:, :, j:j + self.num_frames], resize=(self.p_size, self.p_size))
-                           for j in range(G)], 0)
+        def phasegrams():
+            return torch.cat([phasegram_ops.video_phasegram(attn[:, :, j:j + self.num_frames], resize=(self.p_size, self.p_size))
+                              for j in range(G)], 0)
+        if layers.PARALLEL_BRANCHES and attn.is_cuda:
+            # the phasegrams feed the video encoder only: they start the side-stream branch (layers.run_pair continues it),
+            # so the audio encoder does not wait for them
+            cur, side = torch.cuda.current_stream(attn.device), layers._side_stream(attn.device)
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                pgram = phasegrams()
+            pgram.record_stream(cur)
+        else:
+            pgram = phasegrams()
         xa = torch.cat([x_stft[:, :, self.hpf * j:self.hpf * j + span, :] for j in range(G)], 0)
         ya = torch.cat([y_stft[:, :, self.hpf * j:self.hpf * j + span, :] for j in range(G)], 0)
         nn_ops.BN_GROUPS = G
