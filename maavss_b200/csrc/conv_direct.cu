@@ -1,4 +1,4 @@
-// Register-accumulator ("direct") convolution gradients for the small layers of the fusion encoders
+// Register-accumulator ("direct") convolutions -- forward, data gradient, weight gradient -- for the small layers of the fusion encoders
 // (avse_model.py:427-446,474-502; avse_model_final.py:75-107): few channels, few taps, many positions.
 //
 // The implicit-GEMM kernels (conv_igemm.cu) pay a gather + two barriers per 16 reduction indices and, for the
@@ -10,7 +10,8 @@
 //          atomicAdd per dW element per CTA at the end.
 //   DGRAD  a thread keeps CI input channels of one input position in registers and walks only the taps whose
 //          stride phase matches its position (1/(SD*SH*SW) of them), weights read from a shared-memory copy.
-// Both return 1 when they handled the call and 0 when the layer is outside their envelope (caller falls back to
+//   FWD    (end of file) a thread keeps CO output channels of one output position, weights staged as for DGRAD.
+// Each returns 1 when it handled the call and 0 when the layer is outside its envelope (caller falls back to
 // the implicit-GEMM path).
 #include <stdlib.h>
 #include "common.cuh"
