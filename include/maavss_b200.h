@@ -224,6 +224,20 @@ int maavss_attn_diff_normalise(const float* in, float* out, int clips, int frame
 int maavss_attn_headsum_upsample(const float* cls_rows, float* out, int frames, int heads, int cls_stride,
                                  int grid_h, int grid_w, int patch, void* stream);
 
+/* ---- attention-map cache: raw uint8 / fp16 frames instead of the per-frame JPEG files the
+ * reference writes with torchvision.utils.save_image (av_dataset.py:270-276, save_attn_videos.py:10-19) and reads
+ * back through PIL + ToTensor (av_dataset.py:251-269). */
+#define MAAVSS_CACHE_U8 0  /* save_image's quantiser: (unsigned char)clamp(x*255 + 0.5, 0, 255); read back as u8 / 255 */
+#define MAAVSS_CACHE_F16 1 /* round-to-nearest-even fp16 */
+/* maps[0..n) fp32 (the [0,1] per-frame-normalised output of VideoAttention._inference) -> stored[0..n) in `format`.
+ * maps 16-byte aligned, stored 8-byte aligned.  5 (u8) / 6 (fp16) bytes of HBM traffic per pixel. */
+int maavss_attn_cache_pack(const float* maps, void* stored, long long n, int format, void* stream);
+/* stored (clips, frames, hw) in `format` -> out (clips, frames, hw) fp32: dequantise, then av_dataset.py:323-328 per clip
+ * (diff ? cat(0, diff(attn, dim=0)) : attn, then *= 1/max, the signed max) with no fp32 intermediate: the stored frames are
+ * read twice (max pass, scale pass), 2-4 (u8) / 4-8 (fp16) + 4 bytes per pixel.  workspace: clips * 4 bytes. */
+int maavss_attn_cache_load(const void* stored, int format, float* out, int clips, int frames, long long hw, int diff,
+                           void* workspace, void* stream);
+
 /* ---- DINO ViT-S/8 last-layer attention maps (video_attention.py:38-103 over dino/vision_transformer.py) ----
  * bf16 operands, fp32 accumulation / residual stream.  All GEMM-shaped work runs on tcgen05 tensor cores fed by TMA.
  *

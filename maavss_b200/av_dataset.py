@@ -27,7 +27,7 @@ class AV_Dataset:
                  normalize_output_fft=True, autocontrast=False, compress_audio=False, shuffle_files=True,
                  data_path="./data/raw", max_clip_len=None, gen_stft=True, gen_video=True, wandb_run=None,
                  trim_stft_end=True, return_video_path=False, attn_frames_path=None,
-                 clip_source=None, num_clips=0, attention_extractor=None):
+                 clip_source=None, num_clips=0, attention_extractor=None, attn_cache=None, clip_location=None):
         self.gen_stft, self.gen_video = gen_stft, gen_video
         self.hop, self.audio_sample_len, _ = utilities.calc_hop_size(num_frames, hops_per_frame, framerate, samplerate)
         self.attention_extractor = attention_extractor        # a video_attention.VideoAttention (lazy: needs weights)
@@ -43,6 +43,11 @@ class AV_Dataset:
         self.window = torch.hamming_window(self.fft_len)       # av_dataset.py:106
         self.clip_source, self._num_clips = clip_source, num_clips
         self.save_output_examples = False
+        # raw frame cache in place of <attn_frames_path>/<video>/img_%05d.jpg (av_dataset.py:251-278): an
+        # attn_cache.AttnFrameCache plus clip_location(idx) -> (video_name, clip_idx, frames_in_video), the
+        # `video_clips.get_clip_location` / `video_paths` lookup of av_dataset.py:253-255
+        self.attn_cache, self.clip_location = attn_cache, clip_location
+        self.cache_ratio = [0, 0]                              # [hits, misses], av_dataset.py:96,261,271
 
     def toggle_dataset_mode(self, a, v):
         self.gen_stft, self.gen_video = a, v
@@ -103,6 +108,39 @@ class AV_Dataset:
         attn = self.attention_extractor.inference_device(video)            # (T,1,H,W) cuda
         attn = attn_ops.diff_normalise(attn, self.attn_diff)               # av_dataset.py:323-328
         return attn.permute(1, 0, 2, 3)
+
+    # ---- av_dataset.py:251-283 ----
+    def _cache_key(self, idx):
+        if self.clip_location is None:
+            return f"clip_{idx}", 0, self.num_frames           # every synthetic clip is its own "video"
+        video, clip_idx, total = self.clip_location(idx)
+        return video, self.frame_hop * clip_idx, total         # true_idx, av_dataset.py:257
+
+    def get_frames_cached(self, idx):
+        """-> (attn (1,T,H,W) cuda, video).  A hit reads the stored frames (video is zeros, as av_dataset.py:263); a miss
+        runs the extractor and stores its per-frame maps.  The diff / normalise is the un-cached path's (:323-328), not the
+        shape-changing `torch.diff(attn, )` of :268-269."""
+        if self.attn_cache is None:
+            raise RuntimeError("AV_Dataset was built without attn_cache (attn_cache.AttnFrameCache)")
+        video_name, true_idx, total = self._cache_key(idx)
+        if self.attn_cache.has(video_name, true_idx, self.num_frames):
+            self.cache_ratio[0] += 1
+            attn = self.attn_cache.read([(video_name, true_idx, self.num_frames)], self.attn_diff)[0]
+            return attn, torch.zeros(3, self.num_frames, attn.shape[-2], attn.shape[-1])
+        self.cache_ratio[1] += 1
+        if self.attention_extractor is None:
+            raise RuntimeError("AV_Dataset was built without an attention_extractor (VideoAttention)")
+        video, _ = self.clip_source(idx)
+        maps = self.attention_extractor.inference_device(video)            # (T,1,H,W) cuda, before the diff
+        self.attn_cache.reserve(video_name, total)
+        self.attn_cache.write(video_name, true_idx, maps)
+        attn = attn_ops.diff_normalise(maps, self.attn_diff).permute(1, 0, 2, 3)
+        return attn, video.permute(1, 0, 2, 3)
+
+    def gen_av_example_cached(self, idx):
+        attn, video = self.get_frames_cached(idx)
+        x_stft, y_stft, audio = self.gen_stft_example(idx)
+        return x_stft, y_stft, attn, audio, video
 
     def gen_stft_example(self, idx):
         _, audio = self.clip_source(idx)

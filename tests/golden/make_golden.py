@@ -150,6 +150,36 @@ def golden_phasegram():
     save("phasegram", pgram=pg, pgram_nodiff=pg_nodiff)
 
 
+def golden_attn_cache():
+    """Pins oracle/attn_cache.py: torchvision's own save_image quantiser (through lossless PNG) and ToTensor, plus
+    the size of the JPEG error of the reference's writer (save_attn_videos.save_frames) that the raw cache removes."""
+    import tempfile
+    import torchvision
+    from PIL import Image
+    import save_attn_videos
+    maps = synth.attn_clip(2, 4, 64, 64, seed=61)[:, 0]                    # (2, 4, 64, 64) in [0, 1)
+    maps[0, 0, 0, :8] = torch.tensor([0.0, 1.0, -0.3, 1.7, 0.5 / 255, 1.5 / 255, 127.5 / 255, 254.5 / 255])
+    to_tensor = torchvision.transforms.ToTensor()
+    u8, back, jpg = [], [], []
+    with tempfile.TemporaryDirectory() as d:
+        for c, clip in enumerate(maps):
+            for i, frame in enumerate(clip):
+                path = os.path.join(d, f"f_{c}_{i}.png")
+                torchvision.utils.save_image(frame[None].repeat(3, 1, 1), path)      # av_dataset.py:275-276
+                img = Image.open(path)
+                u8.append(np.asarray(img)[:, :, 0].copy())
+                back.append(to_tensor(img)[0])
+            os.mkdir(os.path.join(d, str(c)))
+            quiet(save_attn_videos.save_frames, clip[None], os.path.join(d, str(c)))  # the reference writer (JPEG)
+            for i in range(clip.shape[0]):
+                jpg.append(to_tensor(Image.open(os.path.join(d, str(c), f"img_{i:05d}.jpg")))[0])
+    u8 = np.stack(u8).reshape(2, 4, 64, 64)
+    back = torch.stack(back).reshape(2, 4, 64, 64)
+    jpg = torch.stack(jpg).reshape(2, 4, 64, 64)
+    save("attn_cache", u8=u8, totensor=back, jpeg_max_err=float((jpg - maps.clamp(0, 1)).abs().max()),
+         raw_max_err=float((back - maps.clamp(0, 1)).abs().max()))
+
+
 def run_model_case(name, model, x_a, x_v, y_a, y_v, loss_coeff=0.001):
     import torch.nn.functional as F
     out = {}
@@ -214,6 +244,6 @@ def golden_models():
 if __name__ == "__main__":
     torch.set_num_threads(8)
     install_shim()
-    which = sys.argv[1:] or ["hop", "audio", "generator", "vit", "phasegram", "models"]
+    which = sys.argv[1:] or ["hop", "audio", "generator", "vit", "phasegram", "attn_cache", "models"]
     for w in which:
         globals()["golden_" + w]()

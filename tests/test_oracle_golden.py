@@ -161,3 +161,24 @@ def test_frames_model(golden):
     m = om.AVFusionFramesOracle([2, 2, 64, 129], [2, 1, 8, 256, 256], 8)
     m.load_state_dict(synth.fill_state_dict(m.state_dict(), seed=53))
     _check_model(g, m, xf, fr, yf[:, :, 32:40], fr[:, :, 4], os.path.join(GOLDEN, "frames_params.txt"))
+
+
+def _attn_cache_maps():
+    maps = synth.attn_clip(2, 4, 64, 64, seed=61)[:, 0]
+    maps[0, 0, 0, :8] = torch.tensor([0.0, 1.0, -0.3, 1.7, 0.5 / 255, 1.5 / 255, 127.5 / 255, 254.5 / 255])
+    return maps
+
+
+def test_attn_cache_quantiser(golden):
+    """oracle/attn_cache.py against torchvision's own save_image -> PNG -> ToTensor run by make_golden.py: bit-exact,
+    including the clamp and the x.5 ties."""
+    from oracle import attn_cache as oc
+    g = golden("attn_cache")
+    maps = _attn_cache_maps()
+    u8 = oc.pack_u8(maps)
+    assert torch.equal(u8, torch.from_numpy(g["u8"]))
+    assert torch.equal(oc.unpack(u8), torch.from_numpy(g["totensor"]))
+    assert float(g["raw_max_err"]) <= 0.5 / 255 + 1e-7 < float(g["jpeg_max_err"])    # what dropping JPEG buys
+    out = oc.load_clips(u8, True)
+    assert out.shape == (2, 4, 64, 64) and float(out[:, 0].abs().max()) == 0.0
+    assert float(out.amax(dim=(1, 2, 3)).min()) == pytest.approx(1.0, abs=1e-6)
