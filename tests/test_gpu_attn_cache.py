@@ -57,6 +57,35 @@ def test_load_matches_oracle(fmt, diff, shape):
     assert torch.equal(out, ref)
 
 
+@pytest.mark.parametrize("fmt", ["uint8", "float16"])
+def test_full_batch_properties(fmt):
+    """Config 4's whole batch (256 clips x 12 x 256 x 256, 805 MB fp32: past the oracle's reach) through properties
+    that need no second implementation: (1) with a 1.0 in every clip the un-differenced load is the plain dequantiser,
+    so packing its output again returns the stored bytes (idempotence); (2) the differenced load telescopes --
+    sum over frames = (last - first frame) / max -- and its per-clip maximum is 1 (fp32: v * (1/v) is within one ulp)."""
+    from maavss_b200 import attn_cache
+    clips, T, H, W = 256, 12, 256, 256
+    maps = torch.rand(clips, T, H, W, device="cuda", generator=torch.Generator("cuda").manual_seed(4))
+    maps[:, 3, 7, 9] = 1.0
+    stored = attn_cache.pack(maps, fmt)
+    del maps
+    plain = attn_cache.load(stored, False)
+    assert torch.equal(attn_cache.pack(plain, fmt), stored)
+    assert float(plain.amax()) == 1.0 and float(plain.amin()) >= 0.0
+    d = attn_cache.load(stored, True)
+    assert float(d[:, 0].abs().max()) == 0.0
+    peak = d.amax(dim=(1, 2, 3))
+    assert float((peak - 1).abs().max()) <= 2 ** -23
+    # telescoping: sum_t d[t] * max = plain[T-1] - plain[0]; recover max from one pixel pair per clip
+    tele = d.sum(dim=1)
+    span = plain[:, -1] - plain[:, 0]
+    del d
+    big = span.flatten(1).abs().argmax(dim=1)
+    idx = torch.arange(clips, device="cuda")
+    scale = span.flatten(1)[idx, big] / tele.flatten(1)[idx, big]           # = the clip's max of the differenced frames
+    assert float((tele * scale.view(-1, 1, 1) - span).abs().max()) < 2e-5
+
+
 def test_load_unaligned_view():
     """A clip batch that starts at an odd byte of the stored buffer takes the scalar path; same numbers."""
     from maavss_b200 import _lib, attn_cache
