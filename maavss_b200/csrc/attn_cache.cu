@@ -4,10 +4,15 @@
 //   * load:  stored frames -> fp32 (uint8 / 255 as ToTensor; fp16 widened), temporal diff with a zero first frame and
 //            the per-clip signed-max normalise of av_dataset.py:323-328, without an fp32 intermediate in HBM.
 // HBM-bound elementwise work: 4 pixels per thread (float4 / uchar4 / 2 x half2), grid-stride, one atomicMax per CTA.
+#include <cooperative_groups.h>
 #include <cuda_fp16.h>
+
+#include <cstdlib>
 
 #include "common.cuh"
 #include "../../include/maavss_b200.h"
+
+namespace cg = cooperative_groups;
 
 namespace {
 
@@ -27,20 +32,33 @@ __device__ __forceinline__ unsigned char pack_u8(float x) {
     return (unsigned char)(int)v;
 }
 
+// ToTensor's k / 255 (correctly rounded) in three issue slots instead of the division's slow path: q = k * fl(1/255) is
+// within one ulp, the exact remainder k - 255 q corrects it (Markstein).  Equal to __fdiv_rn(k, 255) for every byte --
+// checked exhaustively on the host (tests/test_attn_cache_host.py) and on the device (test_load_matches_oracle).
+__device__ __forceinline__ float u8_over_255(unsigned int b) {
+    const float r = 0.0039215688593685627f;
+    const float k = (float)b;
+    const float q = __fmul_rn(k, r);
+    return __fmaf_rn(__fmaf_rn(-q, 255.0f, k), r, q);
+}
+
 struct U8 {
     typedef unsigned char T;
-    static __device__ __forceinline__ float ld(const T* p, size_t i) { return __fdiv_rn((float)p[i], 255.0f); }
-    static __device__ __forceinline__ float4 ld4(const T* p, size_t i) {
-        const uchar4 v = *reinterpret_cast<const uchar4*>(p + i);
-        return make_float4(__fdiv_rn((float)v.x, 255.0f), __fdiv_rn((float)v.y, 255.0f), __fdiv_rn((float)v.z, 255.0f),
-                           __fdiv_rn((float)v.w, 255.0f));
+    static __device__ __forceinline__ float ld(const T* p, size_t i) { return u8_over_255(p[i]); }
+    static __device__ __forceinline__ float4 ld4(const T* p, size_t i) { return cvt4(ldraw(p, i)); }
+    typedef uchar4 Raw;                                                       // 4 stored pixels
+    static __device__ __forceinline__ Raw ldraw(const T* p, size_t i) { return *reinterpret_cast<const uchar4*>(p + i); }
+    static __device__ __forceinline__ float4 cvt4(Raw v) {
+        return make_float4(u8_over_255(v.x), u8_over_255(v.y), u8_over_255(v.z), u8_over_255(v.w));
     }
 };
 struct F16 {
     typedef __half T;
     static __device__ __forceinline__ float ld(const T* p, size_t i) { return __half2float(p[i]); }
-    static __device__ __forceinline__ float4 ld4(const T* p, size_t i) {
-        const uint2 raw = *reinterpret_cast<const uint2*>(p + i);
+    static __device__ __forceinline__ float4 ld4(const T* p, size_t i) { return cvt4(ldraw(p, i)); }
+    typedef uint2 Raw;
+    static __device__ __forceinline__ Raw ldraw(const T* p, size_t i) { return *reinterpret_cast<const uint2*>(p + i); }
+    static __device__ __forceinline__ float4 cvt4(Raw raw) {
         const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&raw.x));
         const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
         return make_float4(a.x, a.y, b.x, b.y);
@@ -127,6 +145,93 @@ __global__ void __launch_bounds__(256) cache_clip_kernel(const typename S::T* __
     }
 }
 
+// One thread-block cluster per clip (grid (CL, clips), cluster (CL, 1, 1)): both passes in one launch.  A thread owns
+// FUSED_U pixel quads and walks the frames with the previous frame's values in registers (one conversion per pixel and
+// pass, the diff costs no second load); the CTA maxima meet through distributed shared memory, so the second read of
+// the clip's stored bytes (0.8 / 1.6 MB) comes from L2 while it is still there -- HBM sees s + 4 bytes per pixel.
+constexpr int FUSED_U = 4;
+constexpr int FUSED_THREADS = 256;
+
+template <class S, bool WRITE>
+__device__ __forceinline__ float fused_pass(const typename S::T* __restrict__ clip, float* __restrict__ o, int T, long long hw,
+                                            int diff, float inv, long long first, long long nthreads) {
+    typedef typename S::Raw Raw;
+    const long long hw4 = hw >> 2;
+    float m = -INFINITY;
+    for (long long q0 = first; q0 < hw4; q0 += nthreads * FUSED_U) {
+        // stored bytes of frame t + 1 are in flight while frame t is converted; the previous frame is kept as stored
+        // bytes too (converted again: the issue slots are free, the registers are not)
+        Raw nxt[FUSED_U], prv[FUSED_U];
+#pragma unroll
+        for (int u = 0; u < FUSED_U; ++u) {
+            const long long q = q0 + u * nthreads;
+            if (q < hw4) nxt[u] = S::ldraw(clip, (size_t)(q << 2));
+        }
+        for (int t = 0; t < T; ++t) {
+            Raw cur[FUSED_U];
+#pragma unroll
+            for (int u = 0; u < FUSED_U; ++u) {
+                cur[u] = nxt[u];
+                const long long q = q0 + u * nthreads;
+                if (t + 1 < T && q < hw4) nxt[u] = S::ldraw(clip, (size_t)(t + 1) * hw + (q << 2));
+            }
+#pragma unroll
+            for (int u = 0; u < FUSED_U; ++u) {
+                const long long q = q0 + u * nthreads;
+                if (q >= hw4) continue;
+                float4 v = S::cvt4(cur[u]);
+                if (diff) {
+                    if (t == 0) {
+                        v = make_float4(0.f, 0.f, 0.f, 0.f);               // the zeros_like(attn[0:1]) pad
+                    } else {
+                        const float4 p = S::cvt4(prv[u]);
+                        v = make_float4(v.x - p.x, v.y - p.y, v.z - p.z, v.w - p.w);
+                    }
+                    prv[u] = cur[u];
+                }
+                if (WRITE)      // streaming store: the fp32 output must not evict other clips' stored bytes from L2
+                    __stcs(reinterpret_cast<float4*>(o + (size_t)t * hw + (q << 2)), make_float4(v.x * inv, v.y * inv, v.z * inv, v.w * inv));
+                else
+                    m = fmaxf(fmaxf(m, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
+            }
+        }
+    }
+    return m;
+}
+
+template <class S>
+__global__ void __launch_bounds__(FUSED_THREADS, 4) cache_clip_fused_kernel(const typename S::T* __restrict__ in, float* __restrict__ out,
+                                                                         int T, long long hw, int diff) {
+    cg::cluster_group cluster = cg::this_cluster();
+    const int ncta = gridDim.x;                                   // = cluster size: blockIdx.x is the rank in the cluster
+    const typename S::T* clip = in + (size_t)blockIdx.y * T * hw;
+    float* o = out + (size_t)blockIdx.y * T * hw;
+    const long long first = (long long)blockIdx.x * FUSED_THREADS + threadIdx.x, nthreads = (long long)ncta * FUSED_THREADS;
+    __shared__ float warp_m[FUSED_THREADS / 32];
+    __shared__ float cta_m;
+    float m = warp_max(fused_pass<S, false>(clip, nullptr, T, hw, diff, 0.f, first, nthreads));
+    if ((threadIdx.x & 31) == 0) warp_m[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        m = warp_m[0];
+#pragma unroll
+        for (int w = 1; w < FUSED_THREADS / 32; ++w) m = fmaxf(m, warp_m[w]);
+        cta_m = m;
+    }
+    cluster.sync();
+    m = -INFINITY;
+    for (int r = 0; r < ncta; ++r) m = fmaxf(m, *cluster.map_shared_rank(&cta_m, r));
+    cluster.sync();                                               // no CTA leaves while a peer still reads its cta_m
+    const float inv = 1.0f / m;                                   // `attn *= 1/torch.max(attn)`: signed max
+    fused_pass<S, true>(clip, o, T, hw, diff, inv, first, nthreads);
+}
+
+// MAAVSS_ATTN_CACHE_FUSED=1 selects the one-launch cluster kernel (default: the two-launch path below).
+bool fused_enabled() {
+    static const int on = [] { const char* e = getenv("MAAVSS_ATTN_CACHE_FUSED"); return e ? atoi(e) : 0; }();
+    return on != 0;
+}
+
 int grid_for(long long items, int clips) {
     long long want = (items + 255) / 256;
     const long long cap = max(1, (maavss_num_sms() * 8 + clips - 1) / max(clips, 1));   // ~8 CTAs per SM over all clips
@@ -139,6 +244,22 @@ int launch_load(const void* stored, float* out, int clips, int frames, long long
     const typename S::T* in = static_cast<const typename S::T*>(stored);
     const bool vec = (hw & 3) == 0 && (reinterpret_cast<uintptr_t>(in) % (4 * sizeof(typename S::T))) == 0 &&
                      (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+    if (vec && fused_enabled()) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(8, clips);
+        cfg.blockDim = dim3(FUSED_THREADS);
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 8;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        MAAVSS_CUDA(cudaLaunchKernelEx(&cfg, cache_clip_fused_kernel<S>, in, out, frames, hw, diff));
+        maavss_count_launch();
+        return MAAVSS_OK;
+    }
     MAAVSS_CUDA(cudaMemsetAsync(workspace, 0, sizeof(unsigned int) * clips, st));   // 0 orders below every float
     const long long items = (long long)frames * (vec ? hw >> 2 : hw);
     dim3 grid(grid_for(items, clips), clips);

@@ -35,3 +35,27 @@ def test_new_cache_arguments(tmp_path):
         AttnFrameCache(str(tmp_path / "x"), capacity=4, fmt="jpeg")
     c = AttnFrameCache(str(tmp_path / "h"), capacity=4, frame_hw=(4, 6), fmt="float16")
     assert c.frames.dtype == np.float16 and c.frames.shape == (4, 4, 6)
+
+
+def test_u8_over_255_without_division_is_exact():
+    """attn_cache.cu's u8_over_255 (q = k * fl(1/255); q += fma(-q, 255, k) * fl(1/255)) restated in exact rational
+    arithmetic: equals the correctly rounded k / 255 of ToTensor for every byte."""
+    from fractions import Fraction
+    r = np.float32(1.0) / np.float32(255.0)
+    assert float(r) == 0.0039215688593685627
+
+    def rn(fr):                                   # Fraction -> nearest fp32 (float() of a Fraction is correctly rounded to
+        d = float(fr)                             # fp64; all values here have <= 53 significant bits before that step)
+        assert Fraction(d) == fr
+        return np.float32(d)
+
+    for k in range(256):
+        kf = np.float32(k)
+        q = np.float32(kf * r)
+        rem = rn(Fraction(float(kf)) - Fraction(float(q)) * 255)
+        assert Fraction(float(rem)) == Fraction(float(kf)) - Fraction(float(q)) * 255      # the remainder is exact in fp32
+        exact = Fraction(float(rem)) * Fraction(float(r)) + Fraction(float(q))
+        lo = np.float32(float(exact))             # fp64 rounding of a 48+-bit sum may double-round: check both neighbours
+        cands = [lo, np.nextafter(lo, np.float32(np.inf)), np.nextafter(lo, np.float32(-np.inf))]
+        best = min(cands, key=lambda c: abs(Fraction(float(c)) - exact))
+        assert best == kf / np.float32(255.0), k
