@@ -35,9 +35,11 @@ __device__ __forceinline__ unsigned char pack_u8(float x) {
 // ToTensor's k / 255 (correctly rounded) in three issue slots instead of the division's slow path: q = k * fl(1/255) is
 // within one ulp, the exact remainder k - 255 q corrects it (Markstein).  Equal to __fdiv_rn(k, 255) for every byte --
 // checked exhaustively on the host (tests/test_attn_cache_host.py) and on the device (test_load_matches_oracle).
-__device__ __forceinline__ float u8_over_255(unsigned int b) {
+// The byte becomes a float without I2F (a quarter-rate pipe: 2 conversions per pixel made the uint8 load issue bound):
+// PRMT drops it into the mantissa of 2^23, one exact subtraction removes the 2^23.
+__device__ __forceinline__ float u8_over_255(unsigned int word, unsigned int sel = 0x7540u) {
     const float r = 0.0039215688593685627f;
-    const float k = (float)b;
+    const float k = __fsub_rn(__uint_as_float(__byte_perm(word, 0x4B000000u, sel)), 8388608.0f);
     const float q = __fmul_rn(k, r);
     return __fmaf_rn(__fmaf_rn(-q, 255.0f, k), r, q);
 }
@@ -49,7 +51,8 @@ struct U8 {
     typedef uchar4 Raw;                                                       // 4 stored pixels
     static __device__ __forceinline__ Raw ldraw(const T* p, size_t i) { return *reinterpret_cast<const uchar4*>(p + i); }
     static __device__ __forceinline__ float4 cvt4(Raw v) {
-        return make_float4(u8_over_255(v.x), u8_over_255(v.y), u8_over_255(v.z), u8_over_255(v.w));
+        const unsigned int w = *reinterpret_cast<const unsigned int*>(&v);
+        return make_float4(u8_over_255(w, 0x7540u), u8_over_255(w, 0x7541u), u8_over_255(w, 0x7542u), u8_over_255(w, 0x7543u));
     }
 };
 struct F16 {
@@ -226,10 +229,13 @@ __global__ void __launch_bounds__(FUSED_THREADS, 4) cache_clip_fused_kernel(cons
     fused_pass<S, true>(clip, o, T, hw, diff, inv, first, nthreads);
 }
 
-// MAAVSS_ATTN_CACHE_FUSED=1 selects the one-launch cluster kernel (default: the two-launch path below).
-bool fused_enabled() {
-    static const int on = [] { const char* e = getenv("MAAVSS_ATTN_CACHE_FUSED"); return e ? atoi(e) : 0; }();
-    return on != 0;
+// The one-launch cluster kernel serves the fp16 store (0.29 ms against 0.46-0.51 ms for 256 clips); the uint8 store
+// stays on the two-launch path below, which is issue bound on the dequantiser either way and measured 0.48 / 0.56 ms
+// against 0.52 / 0.61 ms fused.  MAAVSS_ATTN_CACHE_FUSED=1 / =0 forces one path for both formats (the parity tests run
+// under each); clips whose frames are not a multiple of 4 pixels or are misaligned always take the two-launch path.
+int fused_mode() {
+    static const int mode = [] { const char* e = getenv("MAAVSS_ATTN_CACHE_FUSED"); return e ? (atoi(e) != 0) : -1; }();
+    return mode;
 }
 
 int grid_for(long long items, int clips) {
@@ -244,7 +250,7 @@ int launch_load(const void* stored, float* out, int clips, int frames, long long
     const typename S::T* in = static_cast<const typename S::T*>(stored);
     const bool vec = (hw & 3) == 0 && (reinterpret_cast<uintptr_t>(in) % (4 * sizeof(typename S::T))) == 0 &&
                      (reinterpret_cast<uintptr_t>(out) & 15) == 0;
-    if (vec && fused_enabled()) {
+    if (vec && (fused_mode() == 1 || (fused_mode() < 0 && sizeof(typename S::T) == 2))) {
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(8, clips);
         cfg.blockDim = dim3(FUSED_THREADS);
