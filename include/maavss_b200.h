@@ -234,7 +234,9 @@ int maavss_attn_headsum_upsample(const float* cls_rows, float* out, int frames, 
 int maavss_attn_cache_pack(const float* maps, void* stored, long long n, int format, void* stream);
 /* stored (clips, frames, hw) in `format` -> out (clips, frames, hw) fp32: dequantise, then av_dataset.py:323-328 per clip
  * (diff ? cat(0, diff(attn, dim=0)) : attn, then *= 1/max, the signed max) with no fp32 intermediate: the stored frames are
- * read twice (max pass, scale pass), 2-4 (u8) / 4-8 (fp16) + 4 bytes per pixel.  workspace: clips * 4 bytes. */
+ * read twice (max pass, scale pass) -- by one thread-block cluster per clip in a single launch (fp16) or by two launches
+ * (uint8, and any frame size that is not a multiple of 4 pixels); s + 4 algorithmic bytes per pixel.
+ * workspace: clips * 4 bytes (the two-launch path's per-clip maxima). */
 int maavss_attn_cache_load(const void* stored, int format, float* out, int clips, int frames, long long hw, int diff,
                            void* workspace, void* stream);
 

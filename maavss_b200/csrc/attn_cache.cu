@@ -3,7 +3,8 @@
 //   * pack:  fp32 maps -> uint8 with torchvision.utils.save_image's rounding (x*255 + 0.5, clamp, truncate) or fp16 (rne)
 //   * load:  stored frames -> fp32 (uint8 / 255 as ToTensor; fp16 widened), temporal diff with a zero first frame and
 //            the per-clip signed-max normalise of av_dataset.py:323-328, without an fp32 intermediate in HBM.
-// HBM-bound elementwise work: 4 pixels per thread (float4 / uchar4 / 2 x half2), grid-stride, one atomicMax per CTA.
+// HBM-bound elementwise work: 4 pixels per thread (float4 / uchar4 / 2 x half2), grid-stride, one atomicMax per CTA;
+// the fp16 load runs both passes in one launch, one thread-block cluster per clip (cache_clip_fused_kernel).
 #include <cooperative_groups.h>
 #include <cuda_fp16.h>
 
