@@ -273,6 +273,30 @@ int maavss_vit_cls_attn_row(const float* q, long long ldq, const float* k, long 
 int maavss_video_phasegram(const float* frames, float* out, float* scratch, void* max_ws, int B, int T, int H, int W, int R,
                            long long batch_stride, int diff, int cumulative, int normalize, void* stream);
 
+/* The num_seq accumulation windows of one clip batch stacked along the batch axis (x_stft[:, :, hpf*j : hpf*j + span],
+ * j = 0..G-1, train.py:140-147): x (B, C, T, F) -> out (G*B, C, span, F), out[j*B + b] = x[b, :, j*hop : j*hop + span]. */
+int maavss_stack_windows(const float* x, float* out, int B, int C, int T, int F, int G, int hop, int span, void* stream);
+
+/* The same op split where the reference's own structure lets work be shared: train.py:136-139 calls video_phasegram on
+ * the num_seq overlapping windows attn[:, :, j:j+Tw] of one Tc-frame clip (4 windows of 8 over 12 frames), and everything
+ * before the temporal diff is per frame.
+ *   phasegram_frames       : frames (B, Tc, H, W) -> pflat (B, Tc, R*R), per frame: resize, fft2, spatial fftshift, angle,
+ *                            [cumsum / (2 pi R^2) | (p + pi) / 2 pi].  No batch / time roll.  scratch: B*Tc*R*R floats.
+ *   phasegram_windows_max  : max_ws[j] = float bits of max |window j| for the G windows j = 0..G-1 (frames j .. j+Tw-1):
+ *                            out_j[bd, td] = v(td) - v(td-1) (0 at td = 0) with v(td) = pflat[(bd - batch_roll) mod B][j + (td - Tw/2) mod Tw]
+ *                            -- the batch and time rolls of the all-dims fftshift (utilities.py:210) and the diff (:219-222).
+ *                            batch_roll = B/2 is the reference on one process; a data-parallel rank whose loader already
+ *                            supplies the attention frames of global clip (i - B_global/2) mod B_global passes 0 and
+ *                            all-reduces (MAX, as uint32) max_ws between the two calls (utilities.py:226-227 is a whole-batch max).
+ *   phasegram_windows_write: out (G, B, Tw, R*R) = out_j * (normalize ? 1 / max_ws[j] : 1): the G windows stacked along the
+ *                            batch axis, ready for one batched forward. */
+int maavss_phasegram_frames(const float* frames, float* pflat, float* scratch, int B, int Tc, int H, int W, int R,
+                            long long batch_stride, int cumulative, void* stream);
+int maavss_phasegram_windows_max(const float* pflat, void* max_ws, int B, int Tc, int Tw, int G, int R, int batch_roll, int diff,
+                                 void* stream);
+int maavss_phasegram_windows_write(const float* pflat, const void* max_ws, float* out, int B, int Tc, int Tw, int G, int R,
+                                   int batch_roll, int diff, int normalize, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

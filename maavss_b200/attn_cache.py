@@ -76,6 +76,7 @@ class AttnFrameCache:
             self.index, self.used = {}, 0
             mm_mode = "w+"
         npdt = FORMATS[self.fmt][1]
+        self._readonly = mm_mode == "r"
         self.frames = np.memmap(path, dtype=npdt, mode=mm_mode, shape=(self.capacity, self.H, self.W))
         self.valid = np.memmap(path + ".valid", dtype=np.uint8, mode=mm_mode, shape=(self.capacity,))
         self._stage_in = self._stage_out = self._h2d_done = None
@@ -93,8 +94,12 @@ class AttnFrameCache:
         if self.used + n_frames > self.capacity:
             raise ValueError(f"AttnFrameCache: full ({self.used} + {n_frames} > {self.capacity} frames)")
         first = self.used
+        # slots are handed out once per cache lifetime, but make a stale validity byte impossible anyway (a crash between a
+        # write and the index save of an earlier run would otherwise turn into a hit on another video's frames)
+        self.valid[first:first + n_frames] = 0
         self.index[video] = (first, int(n_frames))
         self.used += int(n_frames)
+        self._save_index()              # the index is on disk before any frame of the video can be marked valid
         return first
 
     def _slots(self, video, start, n):
@@ -110,14 +115,34 @@ class AttnFrameCache:
         s = self._slots(video, start, n)
         return s is not None and bool(np.all(self.valid[s:s + n]))
 
-    def flush(self):
-        self.frames.flush()
-        self.valid.flush()
+    def _save_index(self):
+        if self._readonly:
+            return
         meta = {"format": self.fmt, "capacity": self.capacity, "height": self.H, "width": self.W, "used": self.used,
                 "videos": {k: list(v) for k, v in self.index.items()}}
         tmp = self.path + ".json.tmp"
-        json.dump(meta, open(tmp, "w"))
-        os.replace(tmp, self.path + ".json")
+        with open(tmp, "w") as f:
+            json.dump(meta, f)
+        os.replace(tmp, self.path + ".json")          # atomic: a reader sees the old or the new index, never a torn one
+
+    def flush(self):
+        if self._readonly:
+            return
+        self.frames.flush()
+        self.valid.flush()
+        self._save_index()
+
+    def close(self):
+        """Flush the maps and the index.  Also run from __del__; a cache that is simply dropped loses nothing either, since
+        `reserve` saves the index itself and frame / validity bytes live in shared file mappings."""
+        if getattr(self, "frames", None) is not None:
+            self.flush()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
     # ---- device <-> memmap ----
     def _pinned(self, which, n):

@@ -1,0 +1,45 @@
+// Layout glue of the train steps that PyTorch would run as ATen copy kernels (torch.cat / slice copies): kept inside the
+// library so that every launch of a step is one of ours (DESIGN.md "Execution model").  All HBM / L2 streaming copies.
+#include "common.cuh"
+#include "../../include/maavss_b200.h"
+
+namespace {
+
+// out[(j*B + b), c, t, f] = x[b, c, j*hop + t, f]: every (j, b, c) is one contiguous run of span*F floats.
+template <typename V>
+__global__ void __launch_bounds__(256) stack_windows_kernel(const V* __restrict__ x, V* __restrict__ out, int B, int C,
+                                                            long long plane_in, long long run, long long hop_elems,
+                                                            int chunks_per_run) {
+    const long long blk = blockIdx.x / chunks_per_run;      // (j, b, c)
+    const int chunk = blockIdx.x % chunks_per_run;
+    const int c = (int)(blk % C);
+    const int b = (int)((blk / C) % B);
+    const int j = (int)(blk / ((long long)C * B));
+    const V* src = x + ((long long)b * C + c) * plane_in + (long long)j * hop_elems;
+    V* dst = out + blk * run;
+    for (long long q = (long long)chunk * 256 + threadIdx.x; q < run; q += (long long)chunks_per_run * 256) dst[q] = __ldg(src + q);
+}
+
+}  // namespace
+
+extern "C" int maavss_stack_windows(const float* x, float* out, int B, int C, int T, int F, int G, int hop, int span, void* stream) {
+    if (B == 0 || G == 0) return MAAVSS_OK;
+    MAAVSS_CHECK_ARG(x && out, "stack_windows: null argument");
+    MAAVSS_CHECK_ARG(B > 0 && C > 0 && G > 0 && span > 0 && hop >= 0 && (long long)(G - 1) * hop + span <= T,
+                     "stack_windows: %d windows of %d rows (hop %d) do not fit %d rows", G, span, hop, T);
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long plane = (long long)T * F, run = (long long)span * F, hop_e = (long long)hop * F;
+    const long long runs = (long long)G * B * C;
+    const bool v4 = plane % 4 == 0 && run % 4 == 0 && hop_e % 4 == 0 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)out & 15) == 0;
+    const long long units = v4 ? run / 4 : run;
+    int cpr = (int)((units + 1023) / 1024);
+    if (cpr < 1) cpr = 1;
+    MAAVSS_CHECK_ARG(runs * cpr < (1ll << 31), "stack_windows: grid too large");
+    if (v4)
+        stack_windows_kernel<float4><<<(unsigned)(runs * cpr), 256, 0, st>>>(reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(out),
+                                                                            B, C, plane / 4, run / 4, hop_e / 4, cpr);
+    else
+        stack_windows_kernel<float><<<(unsigned)(runs * cpr), 256, 0, st>>>(x, out, B, C, plane, run, hop_e, cpr);
+    MAAVSS_LAUNCH_CHECK();
+    return MAAVSS_OK;
+}

@@ -196,9 +196,9 @@ __global__ void __launch_bounds__(kPgThreads) phasegram_frame_kernel(PgArgs a) {
         for (int k = 0; k < wid; ++k) woff += warp_tot[k];
         offset = woff + (inc - run);
     }
-    // destination frame after the batch / time fftshift rolls
-    const int bd = (b + a.B / 2) % a.B, td = (t + a.T / 2) % a.T;
-    float* dst = a.pflat + ((size_t)bd * a.T + td) * R * R + (size_t)tid * PER;
+    // stored at the frame's own (b, t): the batch / time rolls of the all-dims fftshift are index arithmetic of the
+    // window kernels below (a clip's frames are shared by its overlapping accumulation windows)
+    float* dst = a.pflat + ((size_t)b * a.T + t) * R * R + (size_t)tid * PER;
     const float two_pi_n = (float)(2.0 * M_PI * (double)(R * R));
     const float pi_f = (float)M_PI, two_pi = (float)(M_PI * 2.0);
 #pragma unroll
@@ -206,17 +206,45 @@ __global__ void __launch_bounds__(kPgThreads) phasegram_frame_kernel(PgArgs a) {
         dst[q] = a.cumulative ? __fdiv_rn(ang[q] + offset, two_pi_n) : __fdiv_rn(ang[q] + pi_f, two_pi);
 }
 
-__global__ void __launch_bounds__(256) pg_diff_max_kernel(const float* __restrict__ p, float* __restrict__ out, int T, long long n,
-                                                          long long total, int diff, unsigned int* __restrict__ mx) {
+// ---- window half.  A "window" j is the reference's attn[:, :, j:j+Tw] (train.py:138-139): out_j[bd, td] is built from
+// the per-frame flat phases pf[(bd - roll) mod B][j + (td - Tw/2) mod Tw] (the batch and time rolls of the all-dims
+// fftshift, utilities.py:210), temporal diff with a zero first frame (:219-222), division by the window's max |.| (:226-227).
+struct WinArgs {
+    const float* pf;        // (B, Tc, n)
+    float* out;             // (G, B, Tw, n)
+    unsigned int* mx;       // (G) float bits of max |.| per window
+    int B, Tc, Tw, G, roll, diff, normalize;
+    int n4;                 // n / 4
+};
+
+__device__ __forceinline__ float4 win_value(const WinArgs& a, long long q4, int& j) {
+    const int pix = (int)(q4 % a.n4);
+    long long f = q4 / a.n4;
+    const int td = (int)(f % a.Tw);
+    f /= a.Tw;
+    const int bd = (int)(f % a.B);
+    j = (int)(f / a.B);
+    const int sb = (bd - a.roll + a.B) % a.B;
+    const int st = (td + a.Tw - a.Tw / 2) % a.Tw;
+    const float4* base = reinterpret_cast<const float4*>(a.pf) + (size_t)sb * a.Tc * a.n4 + pix;
+    float4 v = __ldg(base + (size_t)(j + st) * a.n4);
+    if (a.diff) {
+        if (td == 0) return make_float4(0.f, 0.f, 0.f, 0.f);
+        const int sp = (td - 1 + a.Tw - a.Tw / 2) % a.Tw;
+        const float4 u = __ldg(base + (size_t)(j + sp) * a.n4);
+        v.x -= u.x; v.y -= u.y; v.z -= u.z; v.w -= u.w;
+    }
+    return v;
+}
+
+// one CTA never straddles two windows: per_win4 is a multiple of the 256-thread tile (n4 = 1024)
+__global__ void __launch_bounds__(256) pg_win_max_kernel(WinArgs a, long long per_win4, int ctas_per_win) {
+    const int j = blockIdx.x / ctas_per_win, c = blockIdx.x % ctas_per_win;
     float m = 0.f;
-    for (long long q = (long long)blockIdx.x * 256 + threadIdx.x; q < total; q += (long long)gridDim.x * 256) {
-        float v = p[q];
-        if (diff) {
-            const long long fr = q / n;
-            v = (fr % T == 0) ? 0.f : v - p[q - n];
-        }
-        out[q] = v;
-        m = fmaxf(m, fabsf(v));
+    for (long long q = (long long)c * 256 + threadIdx.x; q < per_win4; q += (long long)ctas_per_win * 256) {
+        int jj;
+        const float4 v = win_value(a, (long long)j * per_win4 + q, jj);
+        m = fmaxf(fmaxf(m, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
     }
     m = warp_max(m);
     __shared__ float sm[8];
@@ -224,13 +252,20 @@ __global__ void __launch_bounds__(256) pg_diff_max_kernel(const float* __restric
     __syncthreads();
     if (threadIdx.x == 0) {
         for (int k = 1; k < 8; ++k) m = fmaxf(m, sm[k]);
-        atomicMax(mx, __float_as_uint(m));
+        atomicMax(a.mx + j, __float_as_uint(m));
     }
 }
 
-__global__ void __launch_bounds__(256) pg_scale_kernel(float* __restrict__ out, long long total, const unsigned int* __restrict__ mx) {
-    const float inv = 1.0f / __uint_as_float(mx[0]);
-    for (long long q = (long long)blockIdx.x * 256 + threadIdx.x; q < total; q += (long long)gridDim.x * 256) out[q] *= inv;
+__global__ void __launch_bounds__(256) pg_win_write_kernel(WinArgs a, long long total4) {
+    for (long long q = (long long)blockIdx.x * 256 + threadIdx.x; q < total4; q += (long long)gridDim.x * 256) {
+        int j;
+        float4 v = win_value(a, q, j);
+        if (a.normalize) {
+            const float inv = 1.0f / __uint_as_float(__ldg(a.mx + j));
+            v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
+        }
+        reinterpret_cast<float4*>(a.out)[q] = v;
+    }
 }
 
 template <int R>
@@ -265,33 +300,77 @@ int launch_frames(const PgArgs& a, cudaStream_t st) {
 
 }  // namespace
 
+static int pg_check(int B, int T, int H, int W, int R, long long batch_stride) {
+    MAAVSS_CHECK_ARG(R == 64, "video_phasegram: resize target %d unsupported (p_size 64, run_config.py:35)", R);
+    const int do_resize = !(H == R && W == R);
+    MAAVSS_CHECK_ARG(!do_resize || (H >= R && W >= R && H <= 16 * R && W <= 16 * R), "video_phasegram: only down-scaling by <= 16 is supported");
+    MAAVSS_CHECK_ARG(batch_stride >= (long long)T * H * W, "video_phasegram: batch_stride smaller than one clip");
+    return MAAVSS_OK;
+}
+
+extern "C" int maavss_phasegram_frames(const float* frames, float* pflat, float* scratch, int B, int T, int H, int W, int R,
+                                       long long batch_stride, int cumulative, void* stream) {
+    if (B == 0 || T == 0) return MAAVSS_OK;
+    MAAVSS_CHECK_ARG(frames && pflat && scratch, "phasegram_frames: null argument");
+    int rc = pg_check(B, T, H, W, R, batch_stride);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int do_resize = !(H == R && W == R);
+    if (do_resize) {
+        rc = launch_resize<64>(frames, scratch, B, T, H, W, batch_stride, st);
+        if (rc) return rc;
+    }
+    PgArgs a{do_resize ? scratch : frames, pflat, B, T, R, R, cumulative, do_resize ? (long long)T * R * R : batch_stride};
+    return launch_frames<64>(a, st);
+}
+
+static int pg_win_args(WinArgs& a, const float* pflat, float* out, void* max_ws, int B, int Tc, int Tw, int G, int R, int batch_roll,
+                       int diff, int normalize) {
+    MAAVSS_CHECK_ARG(pflat && max_ws, "phasegram_windows: null argument");
+    MAAVSS_CHECK_ARG(B > 0 && Tw > 0 && G > 0 && G - 1 + Tw <= Tc, "phasegram_windows: %d windows of %d frames do not fit %d frames", G, Tw, Tc);
+    MAAVSS_CHECK_ARG((R * R) % 1024 == 0, "phasegram_windows: R*R must be a multiple of 1024");
+    a = WinArgs{pflat, out, (unsigned int*)max_ws, B, Tc, Tw, G, ((batch_roll % B) + B) % B, diff, normalize, R * R / 4};
+    return MAAVSS_OK;
+}
+
+extern "C" int maavss_phasegram_windows_max(const float* pflat, void* max_ws, int B, int Tc, int Tw, int G, int R, int batch_roll,
+                                            int diff, void* stream) {
+    WinArgs a;
+    int rc = pg_win_args(a, pflat, nullptr, max_ws, B, Tc, Tw, G, R, batch_roll, diff, 1);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    MAAVSS_CUDA(cudaMemsetAsync(max_ws, 0, sizeof(unsigned int) * G, st));
+    const long long per_win4 = (long long)B * Tw * a.n4;
+    int cpw = (int)((per_win4 + 1023) / 1024);
+    const int cap = (148 * 8 + G - 1) / G;
+    if (cpw > cap) cpw = cap;
+    pg_win_max_kernel<<<G * cpw, 256, 0, st>>>(a, per_win4, cpw);
+    MAAVSS_LAUNCH_CHECK();
+    return MAAVSS_OK;
+}
+
+extern "C" int maavss_phasegram_windows_write(const float* pflat, const void* max_ws, float* out, int B, int Tc, int Tw, int G, int R,
+                                              int batch_roll, int diff, int normalize, void* stream) {
+    WinArgs a;
+    MAAVSS_CHECK_ARG(out, "phasegram_windows_write: null output");
+    int rc = pg_win_args(a, pflat, out, const_cast<void*>(max_ws), B, Tc, Tw, G, R, batch_roll, diff, normalize);
+    if (rc) return rc;
+    const long long total4 = (long long)G * B * Tw * a.n4;
+    int blocks = (int)((total4 + 511) / 512);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    pg_win_write_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(a, total4);
+    MAAVSS_LAUNCH_CHECK();
+    return MAAVSS_OK;
+}
+
 extern "C" int maavss_video_phasegram(const float* frames, float* out, float* scratch, void* max_ws, int B, int T, int H, int W,
                                       int R, long long batch_stride, int diff, int cumulative, int normalize, void* stream) {
     if (B == 0 || T == 0) return MAAVSS_OK;
     MAAVSS_CHECK_ARG(frames && out && scratch && max_ws, "video_phasegram: null argument");
-    MAAVSS_CHECK_ARG(R == 64, "video_phasegram: resize target %d unsupported (p_size 64, run_config.py:35)", R);
-    const int do_resize = !(H == R && W == R);
-    MAAVSS_CHECK_ARG(!do_resize || (H >= R && W >= R && H <= 16 * R && W <= 16 * R), "video_phasegram: only down-scaling by <= 16 is supported");
-    cudaStream_t st = (cudaStream_t)stream;
-    MAAVSS_CHECK_ARG(batch_stride >= (long long)T * H * W, "video_phasegram: batch_stride smaller than one clip");
-    int rc;
-    if (do_resize) {
-        // `out` is free until the diff / max kernel writes it: it holds the resized frames (B*T, R, R) meanwhile
-        rc = launch_resize<64>(frames, out, B, T, H, W, batch_stride, st);
-        if (rc) return rc;
-    }
-    PgArgs a{do_resize ? out : frames, scratch, B, T, R, R, cumulative, do_resize ? (long long)T * R * R : batch_stride};
-    rc = launch_frames<64>(a, st);
+    // `out` is free until the window kernel writes it: it holds the resized frames (B*T, R, R) meanwhile
+    int rc = maavss_phasegram_frames(frames, scratch, out, B, T, H, W, R, batch_stride, cumulative, stream);
     if (rc) return rc;
-    const long long n = (long long)R * R, total = n * B * T;
-    MAAVSS_CUDA(cudaMemsetAsync(max_ws, 0, sizeof(unsigned int), st));
-    int blocks = (int)((total + 2047) / 2048);
-    if (blocks > 148 * 8) blocks = 148 * 8;
-    pg_diff_max_kernel<<<blocks, 256, 0, st>>>(scratch, out, T, n, total, diff, (unsigned int*)max_ws);
-    MAAVSS_LAUNCH_CHECK();
-    if (normalize) {
-        pg_scale_kernel<<<blocks, 256, 0, st>>>(out, total, (const unsigned int*)max_ws);
-        MAAVSS_LAUNCH_CHECK();
-    }
-    return MAAVSS_OK;
+    rc = maavss_phasegram_windows_max(scratch, max_ws, B, T, T, 1, R, B / 2, diff, stream);
+    if (rc) return rc;
+    return maavss_phasegram_windows_write(scratch, max_ws, out, B, T, T, 1, R, B / 2, diff, normalize, stream);
 }

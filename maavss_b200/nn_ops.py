@@ -439,6 +439,15 @@ def mse_loss(a, b):
     return MSEFn.apply(a, b)
 
 
+def stack_windows(x, windows, hop, span):
+    """x (B, C, T, F) -> (windows*B, C, span, F): window j = x[:, :, j*hop : j*hop + span] in rows [j*B, (j+1)*B).  Inputs only (no autograd)."""
+    x = x.detach().contiguous()
+    B, C, T, F = x.shape
+    out = torch.empty(windows * B, C, span, F, device=x.device, dtype=torch.float32)
+    check(lib().maavss_stack_windows(fptr(x), fptr(out), B, C, T, F, windows, hop, span, stream_ptr()))
+    return out
+
+
 def conv(x, weight, bias, stride, padding):
     return ConvFn.apply(x, weight, bias, stride, padding)
 

@@ -88,9 +88,18 @@ class Adam(torch.optim.Optimizer):
         check(lib().maavss_adam_step(fptr(self.flat.data), fptr(self.flat.grad), fptr(self.exp_avg), fptr(self.exp_avg_sq),
                                      self.flat.numel, g["lr"], g["betas"][0], g["betas"][1], g["eps"], g["weight_decay"],
                                      dptr(self.dev_state), self.grad_scale, stream_ptr()))
+        return loss
+
+    def _sync_step_state(self):
+        """The device counter is the truth (a captured train step advances it on every replay without passing through
+        step()); the per-parameter `step` entries of torch.optim.Adam's state layout are filled from it on demand."""
+        self.step_count = int(self.dev_state[0].item())
         for st in self.state.values():
             st["step"] = torch.tensor(float(self.step_count))
-        return loss
+
+    def state_dict(self):
+        self._sync_step_state()
+        return super().state_dict()
 
     def load_state_dict(self, state_dict):
         """Accepts a torch.optim.Adam state_dict: copies the moments into the arenas (keeps the views)."""

@@ -44,9 +44,30 @@ def world_size():
     return _WORLD
 
 
-def shard_bounds(n_items, rank, world):
-    """Contiguous shard [lo, hi) of n_items for `rank`; the first n_items % world ranks get one extra item."""
+def group():
+    """The data-parallel process group (None on one process)."""
+    return _GROUP
+
+
+def rolled_clip_indices(n_global, rank, world):
+    """Global indices of the clips whose ATTENTION frames rank `rank` loads for the train.py path.
+
+    utilities.video_phasegram fft-shifts every axis (utilities.py:210), so on one process the phasegram that meets the
+    audio of clip i is that of clip (i - B//2) mod B of the WHOLE batch (SURVEY 9.5; reproduced, not fixed).  A rank that
+    holds the audio of its contiguous shard [lo, hi) therefore reads the attention frames of
+    (i - n_global//2) mod n_global for i in [lo, hi); its kernels then roll nothing (batch_roll=0) and the window maxima
+    are all-reduced (utilities.py:226-227 normalises by the max of the whole batch)."""
+    lo, hi = shard_bounds(n_global, rank, world)
+    return [(i - n_global // 2) % n_global for i in range(lo, hi)]
+
+
+def shard_bounds(n_items, rank, world, require_even=False):
+    """Contiguous shard [lo, hi) of n_items for `rank`; the first n_items % world ranks get one extra item.
+    require_even: raise unless every rank gets the same count -- the train steps need that (sync-BN partial shapes,
+    the 1/W gradient average and the per-window MSE means all assume equal shards)."""
     base, rem = divmod(n_items, world)
+    if require_even and rem:
+        raise ValueError(f"{n_items} clips do not split evenly over {world} ranks: the data-parallel train steps need equal shards")
     lo = rank * base + min(rank, rem)
     return lo, lo + base + (1 if rank < rem else 0)
 

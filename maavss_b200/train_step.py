@@ -45,19 +45,31 @@ class _TrainStepBase:
 
     def _capture(self, inputs):
         self._static_in = [torch.empty_like(t).copy_(t) for t in inputs]
+        # Warm-up steps (allocator / lazy plan state / NCCL channels) run on a side stream; the training state they touch
+        # -- parameters, Adam moments and step counter, BatchNorm running statistics -- is snapshotted and put back, so
+        # the first replay is the first optimizer step, as in the reference loop.
+        opt = self.opt
+        keep = [t.clone() for t in (opt.flat.data, opt.exp_avg, opt.exp_avg_sq, opt.dev_state)]
+        bufs = [(b, b.clone()) for b in self.model.buffers()]
+        count = opt.step_count
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
-            # warm-up on a side stream (allocator / lazy module state); it advances the weights like real steps do
             for _ in range(self.warmup):
                 self._eager(*self._static_in)
         torch.cuda.current_stream().wait_stream(side)
+        with torch.no_grad():
+            for dst, src in zip((opt.flat.data, opt.exp_avg, opt.exp_avg_sq, opt.dev_state), keep):
+                dst.copy_(src)
+            for b, v in bufs:
+                b.copy_(v)
+        opt.step_count = count
         torch.cuda.synchronize()
         self._graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self._graph):
             self._static_out = self._eager(*self._static_in)
         # the capture itself did not execute: host mirror of the step counter must not count it
-        self.opt.step_count -= 1
+        self.opt.step_count = count
 
     def __call__(self, *inputs):
         if not self.use_graph:
@@ -84,8 +96,9 @@ class FusionTrainStep(_TrainStepBase):
     streamed from HBM once per optimizer step instead of num_seq times and the launch count drops by num_seq."""
 
     def __init__(self, model, optimizer, num_seq=4, num_frames=8, hops_per_frame=8, p_size=64, loss_coeff=0.001,
-                 batch_windows=True, overlap_allreduce=True, **kw):
+                 batch_windows=True, overlap_allreduce=True, global_phasegram=True, **kw):
         super().__init__(model, optimizer, **kw)
+        self.global_phasegram = global_phasegram
         self.num_seq, self.num_frames, self.hpf, self.p_size, self.loss_coeff = num_seq, num_frames, hops_per_frame, p_size, loss_coeff
         self.batch_windows = batch_windows
         self._setup_early_allreduce(overlap_allreduce)
@@ -109,12 +122,19 @@ class FusionTrainStep(_TrainStepBase):
                 x.register_hook(lambda g: (self.early.start() if self._running else None, None)[1])
         m.lstm.register_forward_pre_hook(pre_hook)
 
+    def _pg_kw(self):
+        """Data parallel with global_phasegram: `attn` holds the frames of parallel.rolled_clip_indices (the loader applied
+        the whole-batch roll of utilities.py:210), the kernels roll nothing and the window maxima are all-reduced."""
+        if self.global_phasegram and parallel.world_size() > 1:
+            return dict(batch_roll=0, max_group=parallel.group())
+        return {}
+
     def _windows_batched(self, x_stft, y_stft, attn):
         G, B = self.num_seq, x_stft.shape[0]
         span = self.hpf * self.num_frames
         def phasegrams():
-            return torch.cat([phasegram_ops.video_phasegram(attn[:, :, j:j + self.num_frames], resize=(self.p_size, self.p_size))
-                              for j in range(G)], 0)
+            # the 12 distinct frames of a clip are transformed once, the 4 overlapping windows are index arithmetic
+            return phasegram_ops.video_phasegram_windows(attn, G, self.num_frames, resize=(self.p_size, self.p_size), **self._pg_kw())
         if layers.PARALLEL_BRANCHES and attn.is_cuda:
             # the phasegrams feed the video encoder only: they start the side-stream branch (layers.run_pair continues it),
             # so the audio encoder does not wait for them
@@ -125,8 +145,8 @@ class FusionTrainStep(_TrainStepBase):
             pgram.record_stream(cur)
         else:
             pgram = phasegrams()
-        xa = torch.cat([x_stft[:, :, self.hpf * j:self.hpf * j + span, :] for j in range(G)], 0)
-        ya = torch.cat([y_stft[:, :, self.hpf * j:self.hpf * j + span, :] for j in range(G)], 0)
+        xa = nn_ops.stack_windows(x_stft, G, self.hpf, span)
+        ya = nn_ops.stack_windows(y_stft, G, self.hpf, span)
         nn_ops.BN_GROUPS = G
         try:
             yh_a, yh_v, _ = self.model(xa, pgram)
@@ -147,7 +167,7 @@ class FusionTrainStep(_TrainStepBase):
             return self._windows_batched(x_stft, y_stft, attn)
         loss = a_loss = v_loss = None
         for j in range(self.num_seq):
-            pgram = phasegram_ops.video_phasegram(attn[:, :, j:j + self.num_frames], resize=(self.p_size, self.p_size))
+            pgram = phasegram_ops.video_phasegram(attn[:, :, j:j + self.num_frames], resize=(self.p_size, self.p_size), **self._pg_kw())
             s0 = self.hpf * j
             s1 = s0 + self.hpf * self.num_frames
             yh_a, yh_v, _ = self.model(x_stft[:, :, s0:s1, :], pgram)

@@ -19,34 +19,42 @@ def calc_hop_size(num_frames, hops_per_frame, fps, sr):
 
 
 def save_model(path, model, overwrite=False):
-    if not overwrite and os.path.exists(path):
-        raise FileExistsError(path)
+    """utilities.py:162-166: always overwrites (the reference's `overwrite` handling is commented out, and
+    train_autoencoder.py:131 saves to the same path every epoch)."""
     torch.save(model.state_dict(), path)
 
 
-def save_checkpoint(model_state, opt_state, epoch, loss, cp_dir, name="checkpoint"):
-    """Same dict keys as utilities.py:171-178."""
-    os.makedirs(cp_dir, exist_ok=True)
-    path = os.path.join(cp_dir, f"{name}.pt")
-    torch.save({"epoch": epoch, "model_state_dict": model_state, "optimizer_state_dict": opt_state, "loss": loss}, path)
+def save_checkpoint(model_dict, opt_dict, epoch, loss, name, dir):
+    """utilities.py:168-175, same positional order (train_audio_net.py:130 calls it positionally) and dict keys."""
+    os.makedirs(dir, exist_ok=True)
+    path = f"{dir}/{name}.pt"
+    torch.save({"epoch": epoch, "model_state_dict": model_dict, "optimizer_state_dict": opt_dict, "loss": loss}, path)
     return path
 
 
-def latest_file(directory, pattern="*.pt"):
-    files = glob.glob(os.path.join(directory, pattern))
+def latest_file(dir, ext="pt"):
+    """utilities.py:199-204."""
+    files = glob.glob(f"{dir}/*.{ext}", recursive=True)
     return max(files, key=os.path.getctime) if files else None
 
 
-def load_checkpoint(model, optimizer=None, cp_dir="checkpoints/", auto=True, path=None, load_opt=False):
-    """utilities.py:180-204: strict=False model load, optional optimizer state."""
-    if path is None and auto:
-        path = latest_file(cp_dir)
-    if path is None:
+def load_checkpoint(model, optimizer, dir, auto=True, path=None, load_opt=False):
+    """utilities.py:177-197: the newest *.pt of `dir` (auto) or `path`; strict=False model load; the optimizer state is
+    loaded only on request and a failure there is reported, not raised."""
+    if auto:
+        path = latest_file(dir, "pt")
+        if path is None:
+            print("checkpoint not found, aborting cp load")
+            return None
+    elif path is None:
         return None
     cp = torch.load(path, map_location="cpu")
     model.load_state_dict(cp["model_state_dict"], strict=False)
-    if load_opt and optimizer is not None:
-        optimizer.load_state_dict(cp["optimizer_state_dict"])
+    if load_opt:
+        try:
+            optimizer.load_state_dict(cp["optimizer_state_dict"])
+        except Exception as e:
+            print(f"Error loading optimizer: {e}")
     return cp
 
 

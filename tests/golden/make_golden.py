@@ -118,7 +118,10 @@ def golden_generator():
 def golden_vit():
     import vision_transformer as vits
     import video_attention
-    for tag, depth, T, H, W in (("d12_64", 12, 3, 64, 72), ("d2_256", 2, 2, 256, 256)):
+    only = os.environ.get("GOLDEN_VIT_ONLY")
+    for tag, depth, T, H, W in (("d12_64", 12, 3, 64, 72), ("d2_256", 2, 2, 256, 256), ("d12_256", 12, 4, 256, 256)):
+        if only and tag != only:
+            continue
         sd = synth.vit_state_dict(depth=depth)
         model = vits.VisionTransformer(patch_size=8, embed_dim=384, depth=depth, num_heads=6,
                                        mlp_ratio=4, qkv_bias=True, num_classes=0,

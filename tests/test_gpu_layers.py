@@ -244,6 +244,10 @@ def test_maxpool3d(shape, pk):
     (2, 64, 64, 4, 8, 32, (3, 5, 5), (1, 2, 2)),
     (1, 64, 16, 1, 4, 32, (1, 3, 3), (0, 1, 1)),
     (5, 16, 16, 2, 2, 64, (3, 1, 5), (1, 0, 2)),
+    # the real layers 2-4 of the AV_Fusion_Model_Frames visual encoder at full geometry (avse_model_final.py:39-49), B = 2
+    (2, 16, 32, 8, 128, 128, (3, 5, 5), (1, 2, 2)),
+    (2, 32, 64, 8, 64, 64, (3, 5, 5), (1, 2, 2)),
+    (2, 64, 64, 8, 32, 32, (3, 5, 5), (1, 2, 2)),
 ])
 def test_conv_tensor_core(N, Cin, Cout, D, H, W, k, p):
     """tcgen05 implicit-GEMM convolution (forward and data gradient) vs torch on the same bf16-rounded operands

@@ -76,3 +76,58 @@ def test_phasegram_time_slice_view():
     assert torch.equal(pg, ref)
     orc = op.video_phasegram(attn[:, :, 2:10], resize=(64, 64))
     assert float((pg - orc).abs().median()) < 2e-6
+
+
+def test_phasegram_windows_equal_per_window_calls():
+    """train.py:136-139 calls video_phasegram on 4 overlapping 8-frame windows of a 12-frame clip; the one-pass version
+    transforms each of the 12 frames once and must reproduce the 4 calls bit for bit (same per-frame arithmetic)."""
+    from maavss_b200 import phasegram_ops
+    attn = synth.attn_clip(4, 12, 256, 256, seed=21).cuda()
+    stacked = phasegram_ops.video_phasegram_windows(attn, 4, 8, resize=(64, 64))
+    assert stacked.shape == (16, 1, 8, 4096)
+    for j in range(4):
+        one = phasegram_ops.video_phasegram(attn[:, :, j:j + 8], resize=(64, 64))
+        assert torch.equal(stacked[4 * j:4 * j + 4], one), j
+        orc = op.video_phasegram(attn.cpu()[:, :, j:j + 8], resize=(64, 64))
+        assert float((one.cpu() - orc).abs().median()) < 2e-6
+        assert float(((one.cpu() - orc).abs() > 2e-3).float().mean()) < 2e-3
+    # odd batch / odd window length: rolls are B // 2 and Tw // 2 (torch.fft.fftshift)
+    attn = synth.attn_clip(3, 7, 128, 128, seed=22)
+    st = phasegram_ops.video_phasegram_windows(attn.cuda(), 3, 5, resize=(64, 64)).cpu()
+    for j in range(3):
+        orc = op.video_phasegram(attn[:, :, j:j + 5], resize=(64, 64))
+        assert float((st[3 * j:3 * j + 3] - orc).abs().median()) < 2e-6, j
+
+
+def test_phasegram_sharded_ranks_equal_global_batch():
+    """under data parallelism the whole-batch max (utilities.py:226-227) and the batch-axis roll of the
+    all-dims fftshift (utilities.py:210) must be those of the GLOBAL batch.  Two emulated ranks (loader remap
+    parallel.rolled_clip_indices + batch_roll 0 + max of the per-rank window maxima) == one process on all clips."""
+    from maavss_b200 import parallel, phasegram_ops
+    from maavss_b200._lib import check, dptr, fptr, lib, stream_ptr
+    Bg, world, G, Tw, Tc, R = 6, 2, 4, 8, 12, 64
+    attn = synth.attn_clip(Bg, Tc, 128, 128, seed=23).cuda()
+    whole = phasegram_ops.video_phasegram_windows(attn, G, Tw, resize=(R, R))            # (G*Bg, 1, Tw, R*R)
+    L = lib()
+    shards = []
+    for r in range(world):
+        idx = parallel.rolled_clip_indices(Bg, r, world)
+        f = attn[idx, 0].contiguous()
+        B = f.shape[0]
+        pflat = torch.empty(B, Tc, R * R, device="cuda")
+        scratch = torch.empty_like(pflat)
+        mx = torch.empty(G, device="cuda", dtype=torch.int32)
+        check(L.maavss_phasegram_frames(fptr(f), fptr(pflat), fptr(scratch), B, Tc, 128, 128, R, Tc * 128 * 128, 1, stream_ptr()))
+        check(L.maavss_phasegram_windows_max(fptr(pflat), dptr(mx), B, Tc, Tw, G, R, 0, 1, stream_ptr()))
+        shards.append((B, pflat, mx))
+    gmx = torch.maximum(shards[0][2], shards[1][2])                                      # the MAX all-reduce
+    outs = []
+    for B, pflat, _ in shards:
+        out = torch.empty(G * B, Tw, R * R, device="cuda")
+        check(L.maavss_phasegram_windows_write(fptr(pflat), dptr(gmx), fptr(out), B, Tc, Tw, G, R, 0, 1, 1, stream_ptr()))
+        outs.append(out.view(G, B, Tw, R * R))
+    both = torch.cat(outs, 1).reshape(G * Bg, 1, Tw, R * R)
+    assert torch.equal(both, whole)
+    # and the per-rank-local variant differs (guards the claim): local roll + local max
+    local = phasegram_ops.video_phasegram_windows(attn[:3], G, Tw, resize=(R, R)).view(G, 3, Tw, R * R)
+    assert not torch.equal(local, whole.view(G, Bg, Tw, R * R)[:, :3])

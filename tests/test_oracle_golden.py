@@ -66,7 +66,7 @@ def test_generator_helpers(golden):
     assert torch.equal(oa.cartesian_to_polar(f), t(g["polar"]))
 
 
-@pytest.mark.parametrize("tag,depth,T,H,W", [("d12_64", 12, 3, 64, 72), ("d2_256", 2, 2, 256, 256)])
+@pytest.mark.parametrize("tag,depth,T,H,W", [("d12_64", 12, 3, 64, 72), ("d2_256", 2, 2, 256, 256), ("d12_256", 12, 4, 256, 256)])
 def test_vit_attention_maps(golden, tag, depth, T, H, W):
     g = golden("vit_" + tag)
     sd = synth.vit_state_dict(depth=depth)
