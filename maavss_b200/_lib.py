@@ -9,7 +9,8 @@ import os
 import re
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libmaavss_b200.so")
+# MAAVSS_LIB selects another build of the SAME library (the debug variants of build.py); there is still no fallback.
+LIB_PATH = os.environ.get("MAAVSS_LIB") or os.path.join(HERE, "libmaavss_b200.so")
 HEADER = os.path.join(HERE, "..", "include", "maavss_b200.h")
 
 _lib = None

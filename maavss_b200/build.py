@@ -23,6 +23,41 @@ def _digest(paths):
     return h.hexdigest()
 
 
+# Debug variants: only the listed sources are recompiled with the extra flags (into build_<variant>/), everything else is
+# linked from the product build; the result is maavss_b200/libmaavss_b200_<variant>.so (load it with MAAVSS_LIB=<path>).
+VARIANTS = {
+    # The round-1 STFT fault (DESIGN.md "STFT n_fft 4096 fault"): register-indexed named barriers at the 128-register budget.
+    # stft128 reproduces it; stftdbg is the same kernel with every shared / global access range-checked (0 violations).
+    "stft128": (["stft.cu"], ["-DMAAVSS_STFT_MINBLOCKS=2", "-DMAAVSS_STFT_REG_BARRIER=1", "-DMAAVSS_STFT_MINBLOCKS_DEBUG=1"]),
+    "stftdbg": (["stft.cu"], ["-DMAAVSS_STFT_MINBLOCKS=2", "-DMAAVSS_STFT_REG_BARRIER=1", "-DMAAVSS_STFT_BOUNDS=1"]),
+}
+
+
+def build_variant(name):
+    only, extra = VARIANTS[name]
+    build()
+    vobj = os.path.join(HERE, "build_" + name)
+    os.makedirs(vobj, exist_ok=True)
+    objs = []
+    for src in sorted(glob.glob(os.path.join(CSRC, "*.cu"))):
+        base = os.path.basename(src)
+        if base in only:
+            obj = os.path.join(vobj, base[:-3] + ".o")
+            r = subprocess.run([NVCC, *FLAGS, *extra, "-c", src, "-o", obj], capture_output=True, text=True)
+            if r.returncode != 0:
+                raise RuntimeError(f"nvcc failed for {src}:\n{r.stdout}\n{r.stderr}")
+            open(os.path.join(vobj, "ptxas.log"), "w").write(r.stderr)
+        else:
+            obj = os.path.join(OBJ, base[:-3] + ".o")
+        objs.append(obj)
+    lib = os.path.join(HERE, f"libmaavss_b200_{name}.so")
+    r = subprocess.run([NVCC, "-shared", "-o", lib, *objs, "-lcudart", "-gencode", "arch=compute_100a,code=sm_100a"],
+                       capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    return lib
+
+
 def build(verbose=False, force=False):
     os.makedirs(OBJ, exist_ok=True)
     srcs = sorted(glob.glob(os.path.join(CSRC, "*.cu")))
@@ -59,4 +94,7 @@ def build(verbose=False, force=False):
 
 
 if __name__ == "__main__":
-    print(build(verbose="-v" in sys.argv, force="-f" in sys.argv))
+    if "--variant" in sys.argv:
+        print(build_variant(sys.argv[sys.argv.index("--variant") + 1]))
+    else:
+        print(build(verbose="-v" in sys.argv, force="-f" in sys.argv))

@@ -10,6 +10,14 @@
 #include <math.h>
 #include <stdint.h>
 
+// Every shared / global access of the STFT phase functions goes through these two hooks: plain indexing in the product,
+// range-checked accessors in the bounds-instrumented debug build of stft.cu (-DMAAVSS_STFT_BOUNDS, see DESIGN.md
+// "STFT n_fft 4096 fault").
+#ifndef MAAVSS_AT
+#define MAAVSS_AT(p, i) ((p)[(i)])
+#define MAAVSS_DEREF(ptr) (*(ptr))
+#endif
+
 __device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
 __device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
 __device__ __forceinline__ float2 cmul(float2 a, float2 b) {
@@ -150,7 +158,7 @@ __device__ __forceinline__ void fft_pass(const float2 (&v)[16], int i, const flo
 template <int M>
 __device__ __forceinline__ void fft_reload(float2 (&v)[16], int i, const float2* __restrict__ buf) {
 #pragma unroll
-    for (int m = 0; m < 16; ++m) v[m] = buf[pad_idx(i + m * (M / 16))];
+    for (int m = 0; m < 16; ++m) v[m] = MAAVSS_AT(buf, pad_idx(i + m * (M / 16)));
 }
 
 // Full M-point forward FFT of the 16 values per thread in v (elements i + m*M/16); the natural-
@@ -233,14 +241,14 @@ __device__ __forceinline__ void fft_pass_t(const float2 (&v)[16], int i, const f
         for (int r = 0; r < R; ++r) u[r] = v[b + r * NB];
         if constexpr (NS > 1) {
 #pragma unroll
-            for (int r = 1; r < R; ++r) u[r] = cmul(u[r], ttab[(SLOT0 + b * (R - 1) + (r - 1)) * TPF + i]);
+            for (int r = 1; r < R; ++r) u[r] = cmul(u[r], MAAVSS_AT(ttab, (SLOT0 + b * (R - 1) + (r - 1)) * TPF + i));
         }
         Dft<R>::run(u);
         const int j0 = (j / NS) * (NS * R) + k;
 #pragma unroll
         for (int q = 0; q < R; ++q) {
             const int x = j0 + q * NS;
-            out[PAD ? pad_idx(x) : x] = u[q];
+            MAAVSS_AT(out, PAD ? pad_idx(x) : x) = u[q];
         }
     }
 }

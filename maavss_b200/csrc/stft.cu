@@ -15,6 +15,53 @@
 #include <math.h>
 #include <stdlib.h>
 #include "common.cuh"
+
+// ---- bounds-instrumented debug build (python -m maavss_b200.build --variant stftdbg): every shared / global access of the
+// forward kernel is checked against the CTA's dynamic shared window and the caller's buffers; the first violation is
+// recorded (and the access redirected to a dummy word) instead of faulting.  Used to root-cause the n_fft 4096 fault.
+#ifdef MAAVSS_STFT_BOUNDS
+struct MaavssStftDbg {
+    unsigned long long lo[6], hi[6];     // valid global ranges [lo, hi)
+    int n_ranges;
+    unsigned int count;                  // violations seen
+    int rec[12];                         // first violation: line, blockIdx.x, blockIdx.y, threadIdx.x, is_shared, offset lo/hi, limit, size
+    float4 dummy[2];
+};
+__device__ MaavssStftDbg g_stft_dbg;
+extern __shared__ float2 maavss_dbg_smem[];
+template <typename T>
+__device__ __noinline__ T* maavss_dbg_chk(T* p, int line) {
+    bool ok = false;
+    long long off = 0, limit = 0;
+    int shared = 0;
+    if (__isShared(p)) {
+        shared = 1;
+        unsigned int dyn;
+        asm volatile("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dyn));
+        off = (const char*)p - (const char*)maavss_dbg_smem;
+        limit = dyn;
+        ok = off >= 0 && off + (long long)sizeof(T) <= limit;
+    } else {
+        const unsigned long long a = (unsigned long long)p;
+        for (int r = 0; r < g_stft_dbg.n_ranges; ++r)
+            if (a >= g_stft_dbg.lo[r] && a + sizeof(T) <= g_stft_dbg.hi[r]) ok = true;
+        off = (long long)a;
+    }
+    if (ok) return p;
+    if (atomicAdd(&g_stft_dbg.count, 1u) == 0) {
+        int* r = g_stft_dbg.rec;
+        r[0] = line; r[1] = blockIdx.x; r[2] = blockIdx.y; r[3] = threadIdx.x; r[4] = shared;
+        r[5] = (int)(off & 0xffffffffll); r[6] = (int)(off >> 32); r[7] = (int)limit; r[8] = (int)sizeof(T);
+    }
+    return reinterpret_cast<T*>(const_cast<float4*>(g_stft_dbg.dummy));
+}
+#define MAAVSS_AT(p, i) (*maavss_dbg_chk(&(p)[(i)], __LINE__))
+#define MAAVSS_DEREF(ptr) (*maavss_dbg_chk((ptr), __LINE__))
+#endif
+#ifndef MAAVSS_STFT_MINBLOCKS
+#define MAAVSS_STFT_MINBLOCKS 0      // 0: per-size choice (stft_fwd_kernel); the debug variants pin it
+#endif
+
 #include "stft_phases.cuh"
 #include "../../include/maavss_b200.h"
 
@@ -39,13 +86,28 @@ struct Cfg {
     static constexpr int TTAB = FftShape<M>::NSLOT * TPF;       // float2 entries
 };
 
-// Synchronise the TPF threads that share one frame.
+// Synchronise the TPF threads that share one frame: a warp sync, or one named barrier per frame group (ids 1..4; a CTA holds
+// at most 4 groups of more than one warp).  The id is an IMMEDIATE on purpose.  With `bar.sync %r, n` ptxas cannot tell which
+// barriers the kernel uses and reserves all 16 of the CTA ("used 16 barriers"); the n_fft 4096 / 2048 forward kernels built
+// that way for 128 registers raised an illegal-address error as soon as two CTAs shared an SM and a CTA ran more than one
+// batch of frames (round 1's "known issue").  Bisected on a B200 in round 2 (gpurun_out -> profiles/r2_stft4096_rootcause.txt):
+// every shared / global index of the kernel is in range (bounds-instrumented build, 0 violations), and the fault disappears
+// with immediate ids (3 barriers reserved), with one CTA per SM, or with a CTA-wide barrier -- nothing else was changed.
 template <int TPF>
 __device__ __forceinline__ void group_sync(int fi) {
     if constexpr (TPF <= 32) {
         __syncwarp();
     } else {
+#ifdef MAAVSS_STFT_REG_BARRIER     // debug variants only (build.py): the register-indexed form that faulted
         asm volatile("bar.sync %0, %1;" ::"r"(fi + 1), "n"(TPF) : "memory");
+#else
+        switch (fi) {
+            case 0: asm volatile("bar.sync 1, %0;" ::"n"(TPF) : "memory"); break;
+            case 1: asm volatile("bar.sync 2, %0;" ::"n"(TPF) : "memory"); break;
+            case 2: asm volatile("bar.sync 3, %0;" ::"n"(TPF) : "memory"); break;
+            default: asm volatile("bar.sync 4, %0;" ::"n"(TPF) : "memory"); break;
+        }
+#endif
     }
 }
 
@@ -85,7 +147,10 @@ struct StftArgs {
 };
 
 template <int M>
-__global__ void __launch_bounds__(kFwdThreads, (M <= 256) ? 4 : 3) stft_fwd_kernel(StftArgs a) {
+// CTAs per SM the register budget is set for: shared memory holds 2 CTAs at M = 2048 (97 KB each), so 128 registers cost
+// nothing there and remove the spills of the 80-register build
+__global__ void __launch_bounds__(kFwdThreads, (M <= 256) ? 4 : (MAAVSS_STFT_MINBLOCKS ? MAAVSS_STFT_MINBLOCKS : (M >= 2048 ? 2 : 3)))
+stft_fwd_kernel(StftArgs a) {
     constexpr int TPF = M / 16;
     constexpr int P = kFwdThreads / TPF;
     extern __shared__ float2 smem[];
@@ -95,11 +160,11 @@ __global__ void __launch_bounds__(kFwdThreads, (M <= 256) ? 4 : 3) stft_fwd_kern
     float2* bufs = ttab + Cfg<M>::TTAB;      // P * fft_buf_len(M)
     const float hs = 0.5f * a.scale;
     for (int q = threadIdx.x; q < M; q += kFwdThreads) {
-        tw[q] = a.tw[q];
-        const float2 w = *reinterpret_cast<const float2*>(a.window + 2 * q);
-        wsm[q] = make_float2(w.x * hs, w.y * hs);
+        MAAVSS_AT(tw, q) = MAAVSS_AT(a.tw, q);
+        const float2 w = MAAVSS_DEREF(reinterpret_cast<const float2*>(a.window + 2 * q));
+        MAAVSS_AT(wsm, q) = make_float2(w.x * hs, w.y * hs);
     }
-    for (int q = threadIdx.x; q < Cfg<M>::TTAB; q += kFwdThreads) ttab[q] = a.ttab[q];
+    for (int q = threadIdx.x; q < Cfg<M>::TTAB; q += kFwdThreads) MAAVSS_AT(ttab, q) = MAAVSS_AT(a.ttab, q);
     const int fi = threadIdx.x / TPF, i = threadIdx.x % TPF;
     float2* buf = bufs + fi * fft_buf_len(M);
     const float* clip = a.audio + (size_t)blockIdx.y * a.n_samples;
@@ -267,9 +332,15 @@ int launch_stft(const maavss_stft_plan* p, const StftArgs& a0, int batch, cudaSt
     if (bpc < 1) bpc = 1;
     if (bpc > 16) bpc = 16;
     if (bpc > batches) bpc = batches;
+#ifdef MAAVSS_STFT_MINBLOCKS_DEBUG   // bisect switch of the debug variants only
+    if (const char* e = getenv("MAAVSS_STFT_BPC")) bpc = atoi(e) > 0 ? atoi(e) : bpc;
+#endif
     a.batches_per_cta = (int)bpc;
     dim3 grid(ceil_div(batches, a.batches_per_cta), batch);
-    const size_t smem = sizeof(float2) * (2 * (size_t)M + Cfg<M>::TTAB + (size_t)P * fft_buf_len(M));
+    size_t smem = sizeof(float2) * (2 * (size_t)M + Cfg<M>::TTAB + (size_t)P * fft_buf_len(M));
+#ifdef MAAVSS_STFT_MINBLOCKS_DEBUG   // bisect switch: pad the allocation so that only one CTA fits an SM
+    if (const char* e = getenv("MAAVSS_STFT_SMEM_PAD")) smem += (size_t)atoi(e);
+#endif
     MAAVSS_CUDA(cudaFuncSetAttribute(stft_fwd_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     stft_fwd_kernel<M><<<grid, kFwdThreads, smem, st>>>(a);
     MAAVSS_LAUNCH_CHECK();
@@ -421,9 +492,41 @@ extern "C" int maavss_stft_fwd(const maavss_stft_plan* p, const float* audio, fl
     a.scale = normalized ? (float)(1.0 / sqrt(p->sum_w2)) : 1.0f;
     a.batches_per_cta = 1;
     cudaStream_t st = (cudaStream_t)stream;
+#ifdef MAAVSS_STFT_BOUNDS
+    {
+        const int M = p->n_fft / 2;
+        const void* ptr[5] = {audio, planes, p->tw, p->ttab, p->window};
+        const size_t len[5] = {sizeof(float) * (size_t)batch * n_samples, sizeof(float) * (size_t)batch * 2 * a.T_out * a.F_out,
+                               sizeof(float2) * M, sizeof(float2) * fft_ttab_len(M), sizeof(float) * p->n_fft};
+        MaavssStftDbg cur;
+        MAAVSS_CUDA(cudaMemcpyFromSymbol(&cur, g_stft_dbg, sizeof(cur)));
+        for (int r = 0; r < 5; ++r) {
+            cur.lo[r] = (unsigned long long)ptr[r];
+            cur.hi[r] = cur.lo[r] + len[r];
+        }
+        cur.n_ranges = 5;
+        MAAVSS_CUDA(cudaMemcpyToSymbol(g_stft_dbg, &cur, sizeof(cur)));
+    }
+#endif
     DISPATCH_M(p->n_fft / 2, rc = launch_stft<MM>(p, a, batch, st));
     return rc;
 }
+
+#ifdef MAAVSS_STFT_BOUNDS
+// debug build only (not in the public header): out[0] = violations so far, out[1..9] = the first one's record
+extern "C" int maavss_stft_debug_read(int* out10, int reset) {
+    MaavssStftDbg cur;
+    MAAVSS_CUDA(cudaDeviceSynchronize());
+    MAAVSS_CUDA(cudaMemcpyFromSymbol(&cur, g_stft_dbg, sizeof(cur)));
+    out10[0] = (int)cur.count;
+    for (int q = 0; q < 9; ++q) out10[1 + q] = cur.rec[q];
+    if (reset) {
+        cur.count = 0;
+        MAAVSS_CUDA(cudaMemcpyToSymbol(g_stft_dbg, &cur, sizeof(cur)));
+    }
+    return MAAVSS_OK;
+}
+#endif
 
 extern "C" int maavss_istft_fwd(const maavss_stft_plan* p, const float* planes, float* audio, int batch,
                                 int n_frames, int trim_stft_end, int normalized, int polar, void* stream) {

@@ -32,24 +32,24 @@ __device__ __forceinline__ void stft_load_frame(float2 (&v)[16], int i, const fl
         if ((reinterpret_cast<uintptr_t>(p) & 7) == 0) {
 #pragma unroll
             for (int m = 0; m < 16; ++m) {
-                const float2 x = *reinterpret_cast<const float2*>(p + 2 * m * TPF);
-                const float2 w = wsm[i + m * TPF];
+                const float2 x = MAAVSS_DEREF(reinterpret_cast<const float2*>(p + 2 * m * TPF));
+                const float2 w = MAAVSS_AT(wsm, i + m * TPF);
                 v[m] = make_float2(x.x * w.x, x.y * w.y);
             }
         } else {
 #pragma unroll
             for (int m = 0; m < 16; ++m) {
-                const float2 w = wsm[i + m * TPF];
-                v[m] = make_float2(p[2 * m * TPF] * w.x, p[2 * m * TPF + 1] * w.y);
+                const float2 w = MAAVSS_AT(wsm, i + m * TPF);
+                v[m] = make_float2(MAAVSS_AT(p, 2 * m * TPF) * w.x, MAAVSS_AT(p, 2 * m * TPF + 1) * w.y);
             }
         }
     } else {
 #pragma unroll
         for (int m = 0; m < 16; ++m) {
             const int j = i + m * TPF;
-            const float2 w = wsm[j];
-            v[m] = make_float2(clip[reflect_idx(base + 2 * j, n_samples)] * w.x,
-                               clip[reflect_idx(base + 2 * j + 1, n_samples)] * w.y);
+            const float2 w = MAAVSS_AT(wsm, j);
+            v[m] = make_float2(MAAVSS_AT(clip, reflect_idx(base + 2 * j, n_samples)) * w.x,
+                               MAAVSS_AT(clip, reflect_idx(base + 2 * j + 1, n_samples)) * w.y);
         }
     }
 }
@@ -70,11 +70,11 @@ __device__ __forceinline__ void stft_post_frame(int i, const float2* __restrict_
             if (i != 0) break;
             k = M / 2;
         }
-        const float2 A = buf[pad_idx(k)];
-        const float2 B = buf[pad_idx((M - k) & (M - 1))];
+        const float2 A = MAAVSS_AT(buf, pad_idx(k));
+        const float2 B = MAAVSS_AT(buf, pad_idx((M - k) & (M - 1)));
         const float2 S = make_float2(A.x + B.x, A.y - B.y);   // A + conj(B)
         const float2 D = make_float2(A.x - B.x, A.y + B.y);   // A - conj(B)
-        const float2 WD = cmul(tw[k], D);
+        const float2 WD = cmul(MAAVSS_AT(tw, k), D);
         float2 X0 = make_float2(S.x + WD.y, S.y - WD.x);
         float2 X1 = make_float2(S.x - WD.y, -S.y - WD.x);
         if (polar) {
@@ -82,13 +82,13 @@ __device__ __forceinline__ void stft_post_frame(int i, const float2* __restrict_
             X1 = make_float2(sqrtf(X1.x * X1.x + X1.y * X1.y), atan2f(X1.y, X1.x));
         }
         if (k < F_out) {
-            row0[k] = X0.x;
-            row1[k] = X0.y;
+            MAAVSS_AT(row0, k) = X0.x;
+            MAAVSS_AT(row1, k) = X0.y;
         }
         const int k1 = M - k;
         if (k1 != k && k1 < F_out) {
-            row0[k1] = X1.x;
-            row1[k1] = X1.y;
+            MAAVSS_AT(row0, k1) = X1.x;
+            MAAVSS_AT(row1, k1) = X1.y;
         }
     }
 }

@@ -194,3 +194,32 @@ def test_attn_diff_normalise():
     out = attn_ops.diff_normalise(dec.cuda(), True).cpu()
     ref = ov.attn_diff_normalise(dec, True).permute(1, 0, 2, 3)
     torch.testing.assert_close(out, ref, rtol=1e-6, atol=1e-7, equal_nan=True)
+
+
+@pytest.mark.parametrize("n_fft,hop,clips,n", [(4096, 512, 128, 40000), (4096, 2048, 160, 50001), (2048, 256, 128, 30000)])
+def test_stft_large_nfft_many_clips_canary(n_fft, hop, clips, n):
+    """Round-1 "known issue" (n_fft 4096 forward kernel, illegal address at >= 128 clips): the multi-batch-per-CTA loop with
+    two CTAs per SM.  Root cause and fix are in stft.cu (group_sync: immediate named-barrier ids).  The outputs sit between
+    canaries, every clip is checked against torch.stft, and the inverse round trip must reproduce the 1.5863... gain."""
+    from maavss_b200 import audio_ops
+    g = torch.Generator().manual_seed(n_fft + clips)
+    audio = (torch.randn(clips, n, generator=g) * 0.1).cuda()
+    w = torch.hamming_window(n_fft)
+    T, F = audio_ops.stft_out_dims(n, n_fft, hop, False)
+    pad = 4096
+    raw = torch.full((clips * 2 * T * F + 2 * pad,), float("nan"), device="cuda")
+    planes = raw[pad:-pad].view(clips, 2, T, F)
+    for _ in range(3):                                   # repeated launches: the fault was timing dependent
+        audio_ops.stft_planes(audio, w, n_fft, hop, False, out=planes)
+    torch.cuda.synchronize()
+    assert bool(torch.isnan(raw[:pad]).all()) and bool(torch.isnan(raw[-pad:]).all())
+    assert not bool(torch.isnan(planes).any())
+    wd = w.cuda()
+    ref = torch.stft(audio, n_fft, hop, n_fft, wd, center=True, pad_mode="reflect", return_complex=True) / wd.pow(2).sum().sqrt()
+    ref = torch.view_as_real(ref)[:, :, :-1].permute(0, 3, 2, 1)          # (clips, 2, T, F)
+    err = (planes - ref).abs().amax(dim=(1, 2, 3)) / ref.abs().amax(dim=(1, 2, 3))
+    assert float(err.max()) < 2e-5, (int(err.argmax()), float(err.max()))
+    rec = audio_ops.istft_audio(planes, w, n_fft, hop, False)
+    gain = float(n_fft ** 0.5 / wd.pow(2).sum().sqrt())
+    m = n_fft
+    assert float((rec[:, m:-m] - gain * audio[:, m:rec.shape[1] - m]).abs().max()) < 2e-5 * gain

@@ -46,6 +46,14 @@ def param_digest(model):
     return np.stack(out)
 
 
+def assert_digest_close(names, dig, ref, rtol, atol, cols=slice(None)):
+    """np.testing.assert_allclose over param_digest rows, naming the offending parameters on failure."""
+    a, b = np.asarray(dig)[:, cols], np.asarray(ref)[:, cols]
+    bad = np.argwhere(~np.isclose(a, b, rtol=rtol, atol=atol))
+    msg = "; ".join(f"{names[r]}[col {c}] {a[r, c]!r} vs {b[r, c]!r}" for r, c in bad[:12])
+    assert len(bad) == 0, f"{len(bad)} digest entries differ: {msg}"
+
+
 def micro_step_loss(model, x_a, x_v, y_a, y_v, loss_coeff=0.001, num_seq=4):
     from maavss_b200.nn_ops import mse_loss
     yh_a, yh_v, _ = model(x_a, x_v)
@@ -184,8 +192,9 @@ def test_batched_windows_equal_sequential():
     names = [k for i, k in enumerate(names) if k not in names[:i]]
     mods = dict(m0.named_modules())
     noisy = np.array([k.endswith(".bias") and type(mods[k.rsplit(".", 1)[0]]).__name__.startswith("Conv") for k in names])
-    np.testing.assert_allclose(p1[~noisy], p0[~noisy], rtol=1e-5, atol=1e-7)
-    np.testing.assert_allclose(p1[noisy][:, 1:], p0[noisy][:, 1:], rtol=0, atol=2.5e-5)      # zero-gradient conv biases: Adam on noise
+    nm = np.array(names)
+    assert_digest_close(nm[~noisy], p1[~noisy], p0[~noisy], 1e-5, 1e-7)
+    assert_digest_close(nm[noisy], p1[noisy], p0[noisy], 0, 2.5e-5, slice(1, None))      # zero-gradient conv biases: Adam on noise
     # running_var = E[x^2] - mean^2 amplifies the ~1e-7 summation-order differences between the batch-2 and batch-8
     # split-reduction convolutions when mean^2 >> var (the phasegram encoder's first layers): 1e-3 here, 1e-5 vs the goldens
     for k in bn0:
@@ -265,26 +274,36 @@ def test_frames_model_tensor_core_golden(golden):
     rel = lambda a, b: float((a.float() - b.float()).abs().max()) / max(float(b.float().abs().max()), 1e-12)
     # eval outputs: vs the reference goldens and vs the fp32 kernels
     assert rel(evtc[0].cpu(), t(g["eval_a"])) < 2e-2
-    assert rel(evtc[1][..., ::4].cpu(), t(g["eval_v"])) < 2e-2
+    assert rel(evtc[1].cpu(), t(g["eval_v"])) < 2e-2
     assert rel(evtc[2].cpu(), t(g["eval_fused"])) < 2e-2
     for a, b in zip(evtc, ev32):
         assert rel(a, b) < 2e-2
     np.testing.assert_allclose(ltc, g["losses"], rtol=1e-2)
     np.testing.assert_allclose(ltc, l32, rtol=1e-2)
-    worst = 1.0
+    cosines = {}
     for (k, p), (_, q) in zip(mtc.named_parameters(), m32.named_parameters()):
         if q.grad is None:
             assert p.grad is None, k
             continue
-        if float(q.grad.abs().max()) < 1e-12:           # exactly-zero gradients (none expected in this model)
-            continue
-        c = _cos(p.grad, q.grad)
-        worst = min(worst, c)
-        assert c >= 0.999, (k, c)
-    print("frames tensor-core path: worst per-parameter gradient cosine vs fp32", worst, "losses", ltc, l32)
+        cosines[k] = _cos(p.grad, q.grad)
+    print("frames tensor-core path: per-parameter gradient cosine vs the fp32 kernels")
+    for k, c in cosines.items():
+        print(f"   {k:40s} {c:.6f}")
+    print("   losses tc", ltc, "fp32", l32)
+    # Everything outside the visual encoder sees the bf16 convolutions only through a 3e-3 perturbation of its input:
+    # cosine >= 0.999.  Inside the visual encoder the gradient passes 2-4 hard MaxPool3d layers BELOW a bf16
+    # convolution: a 3e-3 forward perturbation flips the arg-max of a few per cent of the 2x2 / 3x3 windows, and each flip
+    # re-routes a whole gradient element to a neighbouring pixel (the fp32 backends already disagree by ~1e-2 there under
+    # 1e-6 noise, test_frames_model_golden).  That is a property of max-pooling, not of the kernels -- the per-layer tests
+    # hold the tcgen05 forward / dgrad / wgrad to 2e-5 against torch on the same bf16-rounded operands -- so those
+    # parameters are held to the direction only.
+    for k, c in cosines.items():
+        assert c >= (0.95 if k.startswith("visual_encoder") else 0.999), (k, c)
     # gradient norms against the reference goldens (fp32 path is held to 5e-3; bf16 operands: 2e-2)
-    _, norms, _ = grad_digest(mtc)
-    np.testing.assert_allclose(norms, g["grad_norms"], rtol=2e-2, atol=2e-8)
+    gnames, norms, _ = grad_digest(mtc)
+    vis = np.array([k.startswith("visual_encoder") for k in gnames])
+    np.testing.assert_allclose(norms[~vis], np.asarray(g["grad_norms"])[~vis], rtol=5e-3, atol=2e-8)
+    np.testing.assert_allclose(norms[vis], np.asarray(g["grad_norms"])[vis], rtol=5e-2)       # re-routed by pool arg-max flips, see above
 
     # loss trajectory over 20 optimizer steps, 4 accumulation windows each
     xs, ys = (z.cuda() for z in synth.stft_batch(2, 96, 129, seed=71))
@@ -314,13 +333,16 @@ def test_config1_chain_stft_model_istft():
         cfg = run_config.model_args()
     finally:
         sys.argv = argv
-    hop, audio_len, n_frames = utilities.calc_hop_size(cfg.num_frames + cfg.num_seq, cfg.hops_per_frame, cfg.fps, cfg.sr)
+    hop, audio_len, n_frames = utilities.calc_hop_size(cfg.num_frames + cfg.num_seq, cfg.hops_per_frame, cfg.framerate, cfg.samplerate)
     assert (hop, audio_len, n_frames) == (66, 6336, 96)
     audio = synth.audio_clip(audio_len, seed=81)
     attn = synth.attn_clip(1, cfg.num_frames + cfg.num_seq, cfg.framesize, cfg.framesize, seed=83)
     noise = torch.randn(1, 2, 96, 128, generator=synth.gen(85))
-    ds = av_dataset.AV_Dataset(num_frames=cfg.num_frames + cfg.num_seq, fft_len=cfg.fft_len, hops_per_frame=cfg.hops_per_frame,
-                               noise_std=0.1, framerate=cfg.fps, samplerate=cfg.sr)
+    # the dataset exactly as train.py:31-48 builds it from the flags
+    ds = av_dataset.AV_Dataset(num_frames=cfg.num_seq + cfg.num_frames, frame_hop=cfg.frame_hop, framerate=cfg.framerate,
+                               samplerate=cfg.samplerate, fft_len=cfg.fft_len, hops_per_frame=cfg.hops_per_frame,
+                               noise_std=cfg.noise_scalar, use_polar=cfg.use_polar, normalize_input_fft=cfg.normalize_fft,
+                               normalize_output_fft=cfg.normalize_output_fft)
     ref = om.AVFusionOracle([1, 2, 64, 128], [1, 1, 8, 4096], 8)
     sd = synth.fill_state_dict(ref.state_dict(), seed=87)
     ref.load_state_dict(sd)
@@ -328,8 +350,8 @@ def test_config1_chain_stft_model_istft():
     m.load_state_dict(sd)
     # oracle chain
     w = oa.hamming_window(cfg.fft_len)
-    y_ref = oa.stft_planes(audio, w, cfg.fft_len, hop, True, True, normalize_output=True)[None]
-    x_ref = oa.add_noise(y_ref, noise, 0.1)
+    y_ref = oa.stft_planes(audio, w, cfg.fft_len, hop, True, cfg.normalize_fft, normalize_output=cfg.normalize_output_fft)[None]
+    x_ref = oa.add_noise(y_ref, noise, cfg.noise_scalar)
     pg_ref = oph.video_phasegram(attn[:, :, :8], resize=(cfg.p_size, cfg.p_size))
     # device chain
     x, y = ds.gen_stft_batch(audio.cuda()[None], noise.cuda())
@@ -404,9 +426,24 @@ def test_fusion_step_graph_b16_vs_oracle():
     names = [k for i, k in enumerate(names) if k not in names[:i]]
     mods = dict(m.named_modules())
     noisy = np.array([k.endswith(".bias") and type(mods[k.rsplit(".", 1)[0]]).__name__.startswith("Conv") for k in names])
-    dig, ref_dig = param_digest(m), synth.param_digest(ref)
-    np.testing.assert_allclose(dig[~noisy], ref_dig[~noisy], rtol=2e-5, atol=2e-7)
-    np.testing.assert_allclose(dig[noisy][:, 1:], ref_dig[noisy][:, 1:], rtol=0, atol=3.5e-5)
+    # Every entry of every parameter after the 3 steps (both models are in this process; stronger than the digest).  One Adam
+    # step moves an entry by at most lr = 1e-5; where |g| is comparable to eps = 1e-8 (fc layers at B = 16) the move depends
+    # on |g| itself, so the 1e-5 .. 1e-4 relative difference between the two backends' gradients (ten train-mode BatchNorm
+    # layers deep in the phasegram encoder) shows up as up to ~5e-7 per entry.  Gate: 10 % of ONE step's maximum move.  (Sums over million-entry tensors add such differences coherently -- the gradient rows of a Linear
+    # layer share the sign pattern of its LeakyReLU input -- which is why the digest's sum column is not used here.)
+    worst = ("", 0.0)
+    refp = dict(ref.named_parameters())
+    for k, is_noisy in zip(names, noisy):
+        p, q = dict(m.named_parameters())[k], refp[k]
+        d = float((p.detach().cpu() - q.detach()).abs().max())
+        if not is_noisy and d > worst[1]:
+            worst = (k, d)
+        assert d <= (3.5e-5 if is_noisy else 1e-6), (k, d)
+    print("B16 graph step vs oracle: worst per-entry parameter difference after 3 steps", worst)
+    bn_ours = {k: v for k, v in m.state_dict().items() if "running" in k}
+    for k, v in ref.state_dict().items():
+        if "running" in k:
+            torch.testing.assert_close(bn_ours[k].cpu(), v, rtol=1e-3, atol=1e-6)
 
 
 def test_graph_step_checkpoint_roundtrip():
