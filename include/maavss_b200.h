@@ -273,6 +273,27 @@ int maavss_vit_cls_attn_row(const float* q, long long ldq, const float* k, long 
 int maavss_video_phasegram(const float* frames, float* out, float* scratch, void* max_ws, int B, int T, int H, int W, int R,
                            long long batch_stride, int diff, int cumulative, int normalize, void* stream);
 
+/* fp32-accurate GEMM on the tensor cores (3xTF32 on tcgen05.mma.kind::tf32, operands staged by TMA, accumulators in TMEM):
+ *     D[P, Q] = A . B^T (+ bias) (-> act) (+ out),  A: P x K, B: Q x K, everything fp32.
+ * Used for the GEMM-shaped layers of the fusion models whose parity bar is fp32: nn.Linear fc1 / fc2 / a_fc1 / v_fc1 with the
+ * accumulation windows stacked (avse_model.py:550,553,618-627; M = 64 rows) and the Bi-LSTM input projections (:542-543):
+ *   forward        y[M, N]  = x w^T      : A = w  (K-major), B = x  (K-major), transposed output, bias per p
+ *   data gradient  dx[M, K] = dz w       : A = w  (MN-major: stored [N][K]), B = dz (K-major), transposed output
+ *   weight grad.   dw[N, K] += dz^T x    : A = dz (MN-major: stored [M][N]), B = x (MN-major), row-major output, accumulate
+ * a_mn_major / b_mn_major: 0 = the operand is stored [rows][K] with pitch lda / ldb, 1 = stored [K][rows].
+ * out_transposed: 0 -> out[p * ldc + q], 1 -> out[q * ldc + p].  bias: per p (bias_on_q = 0) or per q, may be NULL.
+ * Small products are split along K over the SMs; the partial tiles meet in `workspace` (maavss_gemm_tf32x3_workspace_bytes;
+ * 0 when no split is needed) and are reduced in a fixed order.  Pitches must be multiples of 4 floats, pointers 16-byte
+ * aligned, and Q, ldc multiples of 4 for a row-major output (maavss_gemm_tf32x3_supported). */
+int maavss_gemm_tf32x3_supported(int P, int Q, int K, int a_mn_major, long long lda, int b_mn_major, long long ldb, long long ldc,
+                                 int out_transposed);
+long long maavss_gemm_tf32x3_workspace_bytes(int P, int Q, int K);
+int maavss_gemm_tf32x3(const float* A, int a_mn_major, long long lda, const float* B, int b_mn_major, long long ldb, int P, int Q,
+                       int K, float* out, long long ldc, int out_transposed, const float* bias, int bias_on_q, int act, float slope,
+                       int accumulate, void* workspace, long long workspace_bytes, void* stream);
+/* out[c] (+)= sum_r x[r * cols + c]   (bias gradient of a Linear layer from its (rows, cols) output gradient). */
+int maavss_colsum(const float* x, int rows, long long cols, float* out, int accumulate, void* stream);
+
 /* The num_seq accumulation windows of one clip batch stacked along the batch axis (x_stft[:, :, hpf*j : hpf*j + span],
  * j = 0..G-1, train.py:140-147): x (B, C, T, F) -> out (G*B, C, span, F), out[j*B + b] = x[b, :, j*hop : j*hop + span]. */
 int maavss_stack_windows(const float* x, float* out, int B, int C, int T, int F, int G, int hop, int span, void* stream);

@@ -20,7 +20,34 @@ __global__ void __launch_bounds__(256) stack_windows_kernel(const V* __restrict_
     for (long long q = (long long)chunk * 256 + threadIdx.x; q < run; q += (long long)chunks_per_run * 256) dst[q] = __ldg(src + q);
 }
 
+// out[c] (+)= sum_r x[r * cols + c]: one thread per column walks the rows (coalesced across the warp); rows are few (the 64
+// stacked window rows of a Linear layer's output gradient).
+__global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ x, int rows, long long cols, float* __restrict__ out,
+                                                     int accumulate) {
+    const long long c = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (c >= cols) return;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int r = 0;
+    for (; r + 3 < rows; r += 4) {
+        s0 += __ldg(x + (size_t)r * cols + c);
+        s1 += __ldg(x + (size_t)(r + 1) * cols + c);
+        s2 += __ldg(x + (size_t)(r + 2) * cols + c);
+        s3 += __ldg(x + (size_t)(r + 3) * cols + c);
+    }
+    for (; r < rows; ++r) s0 += __ldg(x + (size_t)r * cols + c);
+    const float s = (s0 + s1) + (s2 + s3);
+    out[c] = accumulate ? out[c] + s : s;
+}
+
 }  // namespace
+
+extern "C" int maavss_colsum(const float* x, int rows, long long cols, float* out, int accumulate, void* stream) {
+    if (cols == 0) return MAAVSS_OK;
+    MAAVSS_CHECK_ARG(x && out && rows >= 0, "colsum: bad argument");
+    colsum_kernel<<<(unsigned)((cols + 255) / 256), 256, 0, (cudaStream_t)stream>>>(x, rows, cols, out, accumulate);
+    MAAVSS_LAUNCH_CHECK();
+    return MAAVSS_OK;
+}
 
 extern "C" int maavss_stack_windows(const float* x, float* out, int B, int C, int T, int F, int G, int hop, int span, void* stream) {
     if (B == 0 || G == 0) return MAAVSS_OK;

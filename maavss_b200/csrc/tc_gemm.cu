@@ -227,8 +227,8 @@ static PFN_encodeTiled get_encode() {
 }
 
 // 2-D row-major (rows, cols) tensor of `esize`-byte elements with row pitch `ld` elements; box = (box_rows, box_cols)
-int maavss_make_tmap_2d(CUtensorMap* map, const void* base, int dtype_code, int esize, long long rows, long long cols, long long ld,
-                        int box_rows, int box_cols) {
+int maavss_make_tmap_2d_swz(CUtensorMap* map, const void* base, int dtype_code, int esize, long long rows, long long cols, long long ld,
+                            int box_rows, int box_cols, int swizzle_code) {
     PFN_encodeTiled enc = get_encode();
     MAAVSS_CHECK_ARG(enc, "cuTensorMapEncodeTiled is unavailable (driver too old?)");
     MAAVSS_CHECK_ARG(((uintptr_t)base & 15) == 0 && (ld * esize) % 16 == 0, "TMA operand must be 16-byte aligned with a 16-byte multiple pitch");
@@ -237,10 +237,15 @@ int maavss_make_tmap_2d(CUtensorMap* map, const void* base, int dtype_code, int 
     cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = enc(map, (CUtensorMapDataType)dtype_code, 2, const_cast<void*>(base), dims, strides, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, (CUtensorMapSwizzle)swizzle_code, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     MAAVSS_CHECK_ARG(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d)", (int)r);
     return MAAVSS_OK;
+}
+
+int maavss_make_tmap_2d(CUtensorMap* map, const void* base, int dtype_code, int esize, long long rows, long long cols, long long ld,
+                        int box_rows, int box_cols) {
+    return maavss_make_tmap_2d_swz(map, base, dtype_code, esize, rows, cols, ld, box_rows, box_cols, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
 template <int BN>

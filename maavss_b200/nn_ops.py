@@ -304,6 +304,62 @@ class MaxPoolFn(torch.autograd.Function):
         return dx, None, None
 
 
+# fp32-accurate tensor-core path (3xTF32 on tcgen05, csrc/tc_gemm3.cu) for the Linear / LSTM-projection products with at
+# least this many rows (the accumulation windows stacked by train_step give M = 64); fewer rows stay on the weight-streaming
+# SIMT kernels (linear_skinny.cu).  Accuracy is fp32 grade, so it is on by default.
+TENSOR_CORE_LINEAR = True
+TC_LINEAR_MIN_ROWS = 32
+
+
+def gemm_tf32x3(A, a_mn, lda, B, b_mn, ldb, P, Q, K, out, ldc, transposed, bias=None, bias_on_q=0, act=ACT_NONE, slope=0.0,
+                accumulate=0):
+    """D[P, Q] = A . B^T through maavss_gemm_tf32x3 (see include/maavss_b200.h); returns False when the shape is outside
+    the kernel's envelope (the caller then uses the SIMT kernels)."""
+    L = lib()
+    if not L.maavss_gemm_tf32x3_supported(P, Q, K, a_mn, lda, b_mn, ldb, ldc, transposed):
+        return False
+    if (A.data_ptr() | B.data_ptr() | out.data_ptr() | (bias.data_ptr() if bias is not None else 0)) & 15:
+        return False
+    nbytes = L.maavss_gemm_tf32x3_workspace_bytes(P, Q, K)
+    ws = torch.empty(max(nbytes, 16) // 4, device=out.device, dtype=torch.float32)
+    check(L.maavss_gemm_tf32x3(fptr(A), a_mn, lda, fptr(B), b_mn, ldb, P, Q, K, fptr(out), ldc, transposed, _opt(bias), bias_on_q, act,
+                               slope, accumulate, fptr(ws), ctypes.c_longlong(nbytes), stream_ptr()))
+    return True
+
+
+def _tc_linear(M):
+    return TENSOR_CORE_LINEAR and M >= TC_LINEAR_MIN_ROWS
+
+
+def linear_fwd_into(x2, weight, bias, y, act=ACT_NONE, slope=0.0):
+    """y[M, N] = act(x2[M, K] weight[N, K]^T + bias)."""
+    M, K = x2.shape
+    N = weight.shape[0]
+    if _tc_linear(M) and gemm_tf32x3(weight, 0, K, x2, 0, K, N, M, K, y, N, 1, bias, 0, act, slope, 0):
+        return
+    check(lib().maavss_linear_fwd(fptr(x2), fptr(weight), _opt(bias), fptr(y), M, N, K, act, slope, stream_ptr()))
+
+
+def linear_dgrad_into(dz, weight, dx2):
+    """dx2[M, K] = dz[M, N] weight[N, K]."""
+    M, N = dz.shape
+    K = weight.shape[1]
+    if _tc_linear(M) and gemm_tf32x3(weight, 1, K, dz, 0, N, K, M, N, dx2, K, 1):
+        return
+    check(lib().maavss_linear_dgrad(fptr(dz), fptr(weight), fptr(dx2), M, N, K, stream_ptr()))
+
+
+def linear_wgrad_into(dz, x2, dw, dbias, accumulate):
+    """dw[N, K] (+)= dz[M, N]^T x2[M, K];  dbias[N] (+)= column sums of dz (dbias may be None)."""
+    M, N = dz.shape
+    K = x2.shape[1]
+    if _tc_linear(M) and gemm_tf32x3(dz, 1, N, x2, 1, K, N, K, M, dw, K, 0, None, 0, ACT_NONE, 0.0, accumulate):
+        if dbias is not None:
+            check(lib().maavss_colsum(fptr(dz), M, N, fptr(dbias), accumulate, stream_ptr()))
+        return
+    check(lib().maavss_linear_wgrad(fptr(dz), fptr(x2), fptr(dw), _opt(dbias), M, N, K, accumulate, stream_ptr()))
+
+
 class LinearActFn(torch.autograd.Function):
     """act(x w^T + b) over the last dimension of x."""
 
@@ -314,7 +370,7 @@ class LinearActFn(torch.autograd.Function):
         M, K = x2.shape
         N = weight.shape[0]
         y = torch.empty(M, N, device=x.device, dtype=torch.float32)
-        check(lib().maavss_linear_fwd(fptr(x2), fptr(weight), _opt(bias), fptr(y), M, N, K, act, slope, stream_ptr()))
+        linear_fwd_into(x2, weight, bias, y, act, slope)
         ctx.cfg = (shp, M, N, K, act, slope)
         ctx.save_for_backward(x2, weight, bias, y)
         return y.reshape(*shp[:-1], N)
@@ -332,18 +388,18 @@ class LinearActFn(torch.autograd.Function):
         dx = gw = gb = None
         if ctx.needs_input_grad[0]:
             dx2 = torch.empty(M, K, device=dz.device, dtype=torch.float32)
-            check(L.maavss_linear_dgrad(fptr(dz), fptr(weight), fptr(dx2), M, N, K, stream_ptr()))
+            linear_dgrad_into(dz, weight, dx2)
             dx = dx2.reshape(shp)
         w_t, w_acc, gw = _grad_slot(weight, ctx.needs_input_grad[1])
         b_t, b_acc, gb = _grad_slot(bias, bias is not None and ctx.needs_input_grad[2])
         if w_t is not None:
             if b_t is not None and b_acc != w_acc:          # mixed: give the bias its own pass below
-                check(L.maavss_linear_wgrad(fptr(dz), fptr(x2), fptr(w_t), _null(), M, N, K, w_acc, stream_ptr()))
-                channel_sum(dz.t().contiguous().reshape(1, N, M), b_t, b_acc)
+                linear_wgrad_into(dz, x2, w_t, None, w_acc)
+                check(L.maavss_colsum(fptr(dz), M, N, fptr(b_t), b_acc, stream_ptr()))
             else:
-                check(L.maavss_linear_wgrad(fptr(dz), fptr(x2), fptr(w_t), _opt(b_t), M, N, K, w_acc, stream_ptr()))
+                linear_wgrad_into(dz, x2, w_t, b_t, w_acc)
         elif b_t is not None:
-            channel_sum(dz.t().contiguous().reshape(1, N, M), b_t, b_acc)
+            check(L.maavss_colsum(fptr(dz), M, N, fptr(b_t), b_acc, stream_ptr()))
         return dx, gw, gb, None, None
 
 
@@ -360,7 +416,7 @@ class LSTMFn(torch.autograd.Function):
         gin = torch.empty(2, B, T, 4 * H, device=dev, dtype=torch.float32)
         x2 = x.reshape(B * T, I)
         for d, w in enumerate((w_ih_f, w_ih_r)):
-            check(L.maavss_linear_fwd(fptr(x2), fptr(w), _null(), fptr(gin[d]), B * T, 4 * H, I, ACT_NONE, 0.0, stream_ptr()))
+            linear_fwd_into(x2, w, None, gin[d].view(B * T, 4 * H))
         gates = torch.empty_like(gin)
         cells = torch.empty(2, B, T, H, device=dev, dtype=torch.float32)
         y = torch.empty(B, T, 2 * H, device=dev, dtype=torch.float32)
@@ -393,14 +449,13 @@ class LSTMFn(torch.autograd.Function):
             dg = dgates[d].reshape(B * T, 4 * H)
             t, acc, grads[i_ih] = _grad_slot(w_ih, ctx.needs_input_grad[i_ih])
             if t is not None:
-                check(L.maavss_linear_wgrad(fptr(dg), fptr(x2), fptr(t), _null(), B * T, 4 * H, I, acc, stream_ptr()))
+                linear_wgrad_into(dg, x2, t, None, acc)
             t, acc, grads[i_hh] = _grad_slot(w_hh, ctx.needs_input_grad[i_hh])
             if t is not None:
-                check(L.maavss_linear_wgrad(fptr(dg), fptr(hprev[d].reshape(B * T, H)), fptr(t), _null(), B * T, 4 * H, H, acc,
-                                            stream_ptr()))
+                linear_wgrad_into(dg, hprev[d].reshape(B * T, H), t, None, acc)
             if ctx.needs_input_grad[0]:
                 part = torch.empty(B * T, I, device=dev, dtype=torch.float32)
-                check(L.maavss_linear_dgrad(fptr(dg), fptr(w_ih), fptr(part), B * T, 4 * H, I, stream_ptr()))
+                linear_dgrad_into(dg, w_ih, part)
                 dx = part if dx is None else dx.add_(part)
         grads[0] = dx.reshape(B, T, I) if dx is not None else None
         return tuple(grads)

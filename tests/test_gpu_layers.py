@@ -287,3 +287,66 @@ def test_conv_tensor_core(N, Cin, Cout, D, H, W, k, p):
     finally:
         ops.TENSOR_CORE_CONV = False
     assert rel_err(wo.grad, 2 * dwb) < 5e-5
+
+
+@pytest.mark.parametrize("P,Q,K,a_mn,b_mn,transposed,extras", [
+    # the Linear layers of avse_model.AV_Fusion_Model with the 4 accumulation windows stacked (M = 64): forward ...
+    (32768, 64, 512, 0, 0, 1, "bias_p+leaky"), (16384, 64, 512, 0, 0, 1, "bias_p+leaky"), (2048, 64, 4096, 0, 0, 1, "bias_p+leaky"),
+    (512, 64, 2048, 0, 0, 1, "bias_p+tanh"),
+    # ... data gradient (the weight is read MN-major, contraction over its rows) ...
+    (512, 64, 32768, 1, 0, 1, ""), (4096, 64, 2048, 1, 0, 1, ""), (2048, 64, 512, 1, 0, 1, ""),
+    # ... weight gradient (both operands MN-major, 64 contraction rows, row-major output accumulated into the arena)
+    (32768, 512, 64, 1, 1, 0, "acc"), (2048, 4096, 64, 1, 1, 0, "acc"), (512, 2048, 64, 1, 1, 0, ""),
+    # Bi-LSTM input projection (B*T = 512 rows) and ragged shapes: tails in P, Q and K, bias on q, sigmoid
+    (1024, 512, 512, 0, 0, 1, ""), (200, 40, 100, 0, 0, 0, "bias_q+sigmoid"), (132, 36, 36, 1, 1, 0, "bias_p"), (96, 36, 64, 0, 1, 1, "bias_q"),
+    (1, 64, 512, 0, 0, 1, ""), (300, 260, 8, 1, 0, 0, "acc"),
+])
+def test_gemm_tf32x3(P, Q, K, a_mn, b_mn, transposed, extras):
+    """3xTF32 tensor-core GEMM (csrc/tc_gemm3.cu) against float64: fp32-grade accuracy (<= 2e-6 of the output maximum, the
+    size of fp32 summation-order noise) for every operand layout, k-split and epilogue the fusion models use."""
+    from maavss_b200 import nn_ops as ops
+    gen = g(40)
+    A = torch.randn((K, P) if a_mn else (P, K), generator=gen).cuda()
+    B = torch.randn((K, Q) if b_mn else (Q, K), generator=gen).cuda()
+    # adversarial magnitudes: a wide dynamic range inside every dot product exercises the hi / lo split
+    A = A * torch.exp2(torch.randint(-6, 7, A.shape, generator=gen).float()).cuda()
+    if "tanh" in extras or "sigmoid" in extras:
+        B = B / (40.0 * K ** 0.5)            # pre-activations of order 1: a saturated output would hide the GEMM's error scale
+    bias_on_q = "bias_q" in extras
+    bias = torch.randn(Q if bias_on_q else P, generator=gen).cuda() if "bias" in extras else None
+    act = ops.ACT_LEAKY if "leaky" in extras else ops.ACT_TANH if "tanh" in extras else ops.ACT_SIGMOID if "sigmoid" in extras else ops.ACT_NONE
+    acc = "acc" in extras
+    shape = (Q, P) if transposed else (P, Q)
+    out0 = torch.randn(shape, generator=gen).cuda()
+    out = out0.clone()
+    ok = ops.gemm_tf32x3(A, a_mn, A.shape[1], B, b_mn, B.shape[1], P, Q, K, out, shape[1], transposed, bias, int(bias_on_q), act, 0.3, int(acc))
+    assert ok
+    Ad = (A.t() if a_mn else A).double().cpu()
+    Bd = (B.t() if b_mn else B).double().cpu()
+    ref = Ad @ Bd.t()
+    if bias is not None:
+        ref = ref + (bias.double().cpu()[None, :] if bias_on_q else bias.double().cpu()[:, None])
+    ref = {ops.ACT_LEAKY: lambda t: F.leaky_relu(t, 0.3), ops.ACT_TANH: torch.tanh, ops.ACT_SIGMOID: torch.sigmoid, ops.ACT_NONE: lambda t: t}[act](ref)
+    if transposed:
+        ref = ref.t()
+    if acc:
+        ref = ref + out0.double().cpu()
+    err = float((out.double().cpu() - ref).abs().max()) / float(ref.abs().max())
+    # fp32 reference error for scale: torch's own fp32 GEMM (TF32 off) on the same operands
+    print(f"tf32x3 P{P} Q{Q} K{K} a_mn{a_mn} b_mn{b_mn}: rel err {err:.2e}")
+    assert err < 2e-6, err
+
+
+def test_gemm_tf32x3_envelope():
+    """Shapes the TMA path cannot address (operand pitch not a multiple of 4 floats, odd Q for a row-major output) are
+    reported as unsupported, and the Linear wrappers then fall back to the fp32 SIMT kernels with the same result."""
+    from maavss_b200 import nn_ops as ops
+    L = ops.lib()
+    assert L.maavss_gemm_tf32x3_supported(128, 64, 512, 0, 512, 0, 512, 128, 1) == 1
+    assert L.maavss_gemm_tf32x3_supported(130, 64, 64, 1, 130, 0, 64, 130, 1) == 0       # MN-major pitch 130
+    assert L.maavss_gemm_tf32x3_supported(128, 33, 64, 0, 64, 0, 64, 33, 0) == 0         # row-major output, Q = 33
+    x = torch.randn(40, 37, generator=g(41)).cuda()          # K = 37: pitch not a multiple of 4 -> SIMT path
+    w = torch.randn(50, 37, generator=g(42)).cuda()
+    y = torch.empty(40, 50, device="cuda")
+    ops.linear_fwd_into(x, w, None, y)
+    assert rel_err(y, x @ w.t()) < 5e-6
