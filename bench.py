@@ -234,6 +234,10 @@ def algorithmic_bytes(name, a):
         B, T, H = (iv(a[i]) for i in ((6, 7, 8) if name.endswith("fwd") else (7, 8, 9)))
         # per direction: W_hh (4H x H), one time slice of gin / gates (B x 4H each), cells, h (B x H each)
         return 4 * 2 * (4 * H * H + 2 * B * 4 * H + 3 * B * H), f"B{B} T{T} H{H}"
+    if name == "maavss_gemm_tf32x3":
+        P, Q, K = iv(a[6]), iv(a[7]), iv(a[8])
+        acc = iv(a[16])
+        return 4 * (P * K + Q * K + (2 if acc else 1) * P * Q), f"P{P} Q{Q} K{K} a_mn{iv(a[1])} b_mn{iv(a[4])}"
     if name == "maavss_phasegram_frames":
         B, T, H, W, R = (iv(a[i]) for i in range(3, 8))
         return 4 * B * T * (H * W + R * R), f"B{B} T{T} {H}x{W}->{R}"

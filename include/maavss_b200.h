@@ -197,6 +197,20 @@ int maavss_lstm_step_fwd(const float* gin, const float* w_hh_fwd, const float* w
 int maavss_lstm_step_bwd(const float* dy, const float* gates, const float* cells, const float* w_hh_fwd, const float* w_hh_rev,
                          float* dgates, float* dcell, int B, int T, int H, int step, void* stream);
 
+/* The whole layer in one call (SURVEY 8b bilstm_fwd / bilstm_bwd): x (B, T, I) -> y (B, T, 2H).  gin / gates (2, B, T, 4H) and
+ * cells (2, B, T, H) are outputs the backward needs (caller-owned).  The input projections and all weight / input gradients
+ * run on the 3xTF32 tensor-core GEMM when B*T >= 32, the T recurrent steps are one launch each.
+ * bilstm_bwd: dgates (2, B, T, 4H) is scratch / output; dx (B, T, I) and the four dw_* (same shapes as the weights) may be
+ * NULL; accumulate != 0 adds into the dw_* (gradient accumulation).  workspace: maavss_bilstm_workspace_bytes(.., backward). */
+long long maavss_bilstm_workspace_bytes(int B, int T, int I, int H, int backward);
+int maavss_bilstm_fwd(const float* x, const float* w_ih_fwd, const float* w_hh_fwd, const float* w_ih_rev, const float* w_hh_rev,
+                      float* gin, float* gates, float* cells, float* y, int B, int T, int I, int H, void* workspace,
+                      long long workspace_bytes, void* stream);
+int maavss_bilstm_bwd(const float* dy, const float* x, const float* w_ih_fwd, const float* w_hh_fwd, const float* w_ih_rev,
+                      const float* w_hh_rev, const float* gates, const float* cells, const float* y, float* dgates, float* dx,
+                      float* dw_ih_fwd, float* dw_hh_fwd, float* dw_ih_rev, float* dw_hh_rev, int accumulate, int B, int T, int I, int H,
+                      void* workspace, long long workspace_bytes, void* stream);
+
 /* nn.MSELoss (mean): loss[0] = mean((a - b)^2)   (train.py:154-156).  workspace: maavss_reduce_workspace_bytes(8). */
 int maavss_mse_fwd(const float* a, const float* b, long long n, float* loss, void* workspace, void* stream);
 /* da (+)= gout[0] * 2 (a - b) / n   (gout is a device scalar: no host sync). */
@@ -266,6 +280,28 @@ int maavss_f32_to_bf16(const float* in, void* out_bf16, long long n, void* strea
 int maavss_vit_cls_attn_row(const float* q, long long ldq, const float* k, long long ldk, float* out, int T, int heads, int N,
                             float scale, void* stream);
 
+/* ---- the whole extractor as one call: VideoAttention.__load_model / _inference (video_attention.py:38-160).
+ * vit_create copies the weights into a plan (GEMM weights as bf16).  All pointers are DEVICE fp32 tensors in dino's
+ * state_dict layout: cls_token (dim), pos_embed (1 + pos_grid^2, dim), patch_embed.proj.weight (dim, in_chans*patch*patch),
+ * .bias (dim); block_tensors = a HOST array of depth*12 device pointers, per block: norm1.weight, norm1.bias, attn.qkv.weight,
+ * attn.qkv.bias, attn.proj.weight, attn.proj.bias, norm2.weight, norm2.bias, mlp.fc1.weight, mlp.fc1.bias, mlp.fc2.weight,
+ * mlp.fc2.bias.  head_dim is 64 (vit_tiny / small / base), LayerNorm eps 1e-6 (dino/vision_transformer.py:229-254).
+ * vit_prepare evaluates interpolate_pos_encoding (:174-194, bicubic, the +0.1 trick) for one input size, once.
+ * vit_attn_maps: frames (T, in_chans, H, W) -> out (T, gh*patch, gw*patch):
+ *   post 0: the reference `_inference` output (heads summed, nearest x patch upsample, each frame / its max);
+ *   post 1 / 2: followed by av_dataset.py:323-328 per clip of T/clips frames (2 = with the temporal frame difference).
+ * workspace: maavss_vit_workspace_bytes(plan, T, H, W, clips), caller-owned. */
+typedef struct maavss_vit_plan maavss_vit_plan;
+int maavss_vit_create(maavss_vit_plan** plan, int dim, int depth, int patch, int in_chans, int pos_grid, const float* cls_token,
+                      const float* pos_embed, const float* patch_w, const float* patch_b, const float* const* block_tensors);
+void maavss_vit_destroy(maavss_vit_plan* plan);
+int maavss_vit_prepare(maavss_vit_plan* plan, int H, int W);
+long long maavss_vit_workspace_bytes(const maavss_vit_plan* plan, int T, int H, int W, int clips);
+/* copies the prepared (1 + gh*gw, dim) position embedding of that size to `out` (tests). */
+int maavss_vit_pos_embed(const maavss_vit_plan* plan, int H, int W, float* out);
+int maavss_vit_attn_maps(const maavss_vit_plan* plan, const float* frames, int T, int H, int W, float* out, int post, int clips,
+                         void* workspace, long long workspace_bytes, void* stream);
+
 /* utilities.video_phasegram (utilities.py:206-228; called on every micro-step, train.py:139):
  * frames (B, T, H, W) with clip stride batch_stride (elements) -> out (B, T, R*R): antialiased bilinear resize to (R, R), fft2, fftshift over all four dims,
  * angle, flatten, [cumsum / (2 pi R^2) | (p + pi) / 2 pi], [temporal diff with a zero first frame], [/ max |.| over the
@@ -317,6 +353,24 @@ int maavss_phasegram_windows_max(const float* pflat, void* max_ws, int B, int Tc
                                  void* stream);
 int maavss_phasegram_windows_write(const float* pflat, const void* max_ws, float* out, int B, int Tc, int Tw, int G, int R,
                                    int batch_roll, int diff, int normalize, void* stream);
+
+/* ------------------------------------------------------------- data parallel ---------- */
+/* One NCCL communicator over the GPUs of the box (one process per GPU).  Rank 0 calls comm_unique_id (128 bytes) and hands
+ * the bytes to every rank (any side channel: torch.distributed store, MPI, a file); every rank then calls comm_init with its
+ * CUDA device current.  NCCL itself is loaded at run time (libnccl.so.2).  The reference is single-process: these are the
+ * collectives its loop needs to run N ranks == one process on the concatenated batch:
+ *   grad_allreduce     in-place SUM of the flat fp32 gradient arena after the num_seq accumulation windows (train.py:158-161);
+ *                      the 1/world average is maavss_adam_step's grad_scale
+ *   allreduce_sum_f64  train-mode BatchNorm partial sums between bn_reduce and bn_apply (statistics of the global batch)
+ *   allreduce_max_u32  the whole-batch max of utilities.video_phasegram (utilities.py:226-227), float bits as uint32
+ * All three enqueue on `stream` (capturable into the train step's CUDA graph). */
+typedef struct maavss_comm maavss_comm;
+int maavss_comm_unique_id(void* id128);
+int maavss_comm_init(maavss_comm** comm, int rank, int world, const void* id128);
+void maavss_comm_destroy(maavss_comm* comm);
+int maavss_grad_allreduce(maavss_comm* comm, float* grad, long long n, void* stream);
+int maavss_allreduce_sum_f64(maavss_comm* comm, double* v, long long n, void* stream);
+int maavss_allreduce_max_u32(maavss_comm* comm, void* words, long long n, void* stream);
 
 #ifdef __cplusplus
 }

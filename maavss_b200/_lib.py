@@ -76,7 +76,9 @@ class _Profiler:
     """Optional per-call device timing (CUDA events on the launching stream) used by bench.py's roofline leg."""
     SKIP = {"maavss_last_error", "maavss_abi_version", "maavss_device_sm_count", "maavss_launch_count", "maavss_bn_splits",
             "maavss_reduce_workspace_bytes", "maavss_stft_out_dims", "maavss_stft_plan_create", "maavss_stft_plan_destroy",
-            "maavss_dft_plan_create", "maavss_dft_plan_destroy"}
+            "maavss_dft_plan_create", "maavss_dft_plan_destroy", "maavss_gemm_tf32x3_supported", "maavss_gemm_tf32x3_workspace_bytes",
+            "maavss_conv_tc_supported", "maavss_conv_tc_workspace_bytes", "maavss_conv_wgrad_tc_supported",
+            "maavss_conv_wgrad_tc_workspace_bytes"}
 
     def __init__(self, real):
         self.real, self.records = real, []

@@ -51,7 +51,7 @@ def build_variant(name):
             obj = os.path.join(OBJ, base[:-3] + ".o")
         objs.append(obj)
     lib = os.path.join(HERE, f"libmaavss_b200_{name}.so")
-    r = subprocess.run([NVCC, "-shared", "-o", lib, *objs, "-lcudart", "-gencode", "arch=compute_100a,code=sm_100a"],
+    r = subprocess.run([NVCC, "-shared", "-o", lib, *objs, "-lcudart", "-ldl", "-gencode", "arch=compute_100a,code=sm_100a"],
                        capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
@@ -86,7 +86,7 @@ def build(verbose=False, force=False):
         f.write(log)
     newest = max(os.path.getmtime(o) for o in objs)
     if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < newest:
-        r = subprocess.run([NVCC, "-shared", "-o", LIB, *objs, "-lcudart", "-gencode", "arch=compute_100a,code=sm_100a"],
+        r = subprocess.run([NVCC, "-shared", "-o", LIB, *objs, "-lcudart", "-ldl", "-gencode", "arch=compute_100a,code=sm_100a"],
                            capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

@@ -198,3 +198,132 @@ extern "C" int maavss_lstm_step_bwd(const float* dy, const float* gates, const f
     MAAVSS_LAUNCH_CHECK();
     return MAAVSS_OK;
 }
+
+// ------------------------------------------------------------------------------------------------------------------
+// Whole-layer entry points (bilstm_fwd / bilstm_bwd): input projections, the T recurrent steps, and in the
+// backward the h_{t-1} gather, the four weight gradients and the input gradient, all enqueued by one C call.
+namespace {
+
+// hprev[d][b][t][:] = h of the step BEFORE t in direction d (zeros at the direction's first step), from y (B, T, 2H)
+__global__ void __launch_bounds__(256) lstm_hprev_kernel(const float* __restrict__ y, float* __restrict__ hprev, int B, int T, int H4) {
+    const long long n = 2LL * B * T * H4;            // float4 units
+    for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < n; e += (long long)gridDim.x * 256) {
+        const int c4 = (int)(e % H4);
+        long long r = e / H4;
+        const int t = (int)(r % T);
+        r /= T;
+        const int b = (int)(r % B), d = (int)(r / B);
+        const int tp = d ? t + 1 : t - 1;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (tp >= 0 && tp < T) v = __ldg(reinterpret_cast<const float4*>(y + ((size_t)b * T + tp) * 8 * H4 + (size_t)d * 4 * H4) + c4);
+        reinterpret_cast<float4*>(hprev)[e] = v;
+    }
+}
+
+inline size_t al256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+// y[M, N] = x w^T on the 3xTF32 tensor-core GEMM when the shape allows, else the SIMT kernels
+int proj_fwd(const float* x, const float* w, float* y, int M, int N, int K, void* ws, long long ws_bytes, void* st) {
+    if (M >= 32 && maavss_gemm_tf32x3_supported(N, M, K, 0, K, 0, K, N, 1) && maavss_gemm_tf32x3_workspace_bytes(N, M, K) <= ws_bytes)
+        return maavss_gemm_tf32x3(w, 0, K, x, 0, K, N, M, K, y, N, 1, nullptr, 0, MAAVSS_ACT_NONE, 0.f, 0, ws, ws_bytes, st);
+    return maavss_linear_fwd(x, w, nullptr, y, M, N, K, MAAVSS_ACT_NONE, 0.f, st);
+}
+int proj_wgrad(const float* dz, const float* x, float* dw, int M, int N, int K, int accumulate, void* ws, long long ws_bytes, void* st) {
+    if (M >= 32 && maavss_gemm_tf32x3_supported(N, K, M, 1, N, 1, K, K, 0) && maavss_gemm_tf32x3_workspace_bytes(N, K, M) <= ws_bytes)
+        return maavss_gemm_tf32x3(dz, 1, N, x, 1, K, N, K, M, dw, K, 0, nullptr, 0, MAAVSS_ACT_NONE, 0.f, accumulate, ws, ws_bytes, st);
+    return maavss_linear_wgrad(dz, x, dw, nullptr, M, N, K, accumulate, st);
+}
+
+}  // namespace
+
+extern "C" long long maavss_bilstm_workspace_bytes(int B, int T, int I, int H, int backward) {
+    const int M = B * T;
+    long long g = maavss_gemm_tf32x3_workspace_bytes(4 * H, M, I);
+    if (backward) {
+        const long long c[] = {maavss_gemm_tf32x3_workspace_bytes(4 * H, I, M), maavss_gemm_tf32x3_workspace_bytes(4 * H, H, M),
+                               maavss_gemm_tf32x3_workspace_bytes(I, M, 4 * H)};
+        for (long long v : c) g = v > g ? v : g;
+        // + dcell (2, B, H), hprev (2, B, T, H), dx partial (B*T, I)
+        return (long long)(al256((size_t)g) + al256(sizeof(float) * 2 * (size_t)B * H) + al256(sizeof(float) * 2 * (size_t)M * H) +
+                           al256(sizeof(float) * (size_t)M * I)) + 256;
+    }
+    return (long long)al256((size_t)g) + 256;
+}
+
+extern "C" int maavss_bilstm_fwd(const float* x, const float* w_ih_fwd, const float* w_hh_fwd, const float* w_ih_rev, const float* w_hh_rev,
+                                 float* gin, float* gates, float* cells, float* y, int B, int T, int I, int H, void* workspace,
+                                 long long workspace_bytes, void* stream) {
+    if (B == 0 || T == 0) return MAAVSS_OK;
+    MAAVSS_CHECK_ARG(x && w_ih_fwd && w_hh_fwd && w_ih_rev && w_hh_rev && gin && gates && cells && y, "bilstm_fwd: null argument");
+    MAAVSS_CHECK_ARG(workspace_bytes >= maavss_bilstm_workspace_bytes(B, T, I, H, 0), "bilstm_fwd: workspace too small");
+    void* ws = (void*)(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
+    const long long wsb = workspace_bytes - 256;
+    const int M = B * T;
+    int rc = proj_fwd(x, w_ih_fwd, gin, M, 4 * H, I, ws, wsb, stream);
+    if (rc) return rc;
+    rc = proj_fwd(x, w_ih_rev, gin + (size_t)M * 4 * H, M, 4 * H, I, ws, wsb, stream);
+    if (rc) return rc;
+    for (int s = 0; s < T; ++s) {
+        rc = maavss_lstm_step_fwd(gin, w_hh_fwd, w_hh_rev, gates, cells, y, B, T, H, s, stream);
+        if (rc) return rc;
+    }
+    return MAAVSS_OK;
+}
+
+extern "C" int maavss_bilstm_bwd(const float* dy, const float* x, const float* w_ih_fwd, const float* w_hh_fwd, const float* w_ih_rev,
+                                 const float* w_hh_rev, const float* gates, const float* cells, const float* y, float* dgates, float* dx,
+                                 float* dw_ih_fwd, float* dw_hh_fwd, float* dw_ih_rev, float* dw_hh_rev, int accumulate, int B, int T,
+                                 int I, int H, void* workspace, long long workspace_bytes, void* stream) {
+    if (B == 0 || T == 0) return MAAVSS_OK;
+    MAAVSS_CHECK_ARG(dy && x && w_ih_fwd && w_hh_fwd && w_ih_rev && w_hh_rev && gates && cells && y && dgates, "bilstm_bwd: null argument");
+    MAAVSS_CHECK_ARG(workspace_bytes >= maavss_bilstm_workspace_bytes(B, T, I, H, 1), "bilstm_bwd: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int M = B * T;
+    uint8_t* base = (uint8_t*)(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
+    long long g = maavss_bilstm_workspace_bytes(B, T, I, H, 1) - 256 - (long long)(al256(sizeof(float) * 2 * (size_t)B * H) +
+                  al256(sizeof(float) * 2 * (size_t)M * H) + al256(sizeof(float) * (size_t)M * I));
+    void* gws = base;
+    float* dcell = (float*)(base + g);
+    float* hprev = (float*)((uint8_t*)dcell + al256(sizeof(float) * 2 * (size_t)B * H));
+    MAAVSS_CUDA(cudaMemsetAsync(dcell, 0, sizeof(float) * 2 * (size_t)B * H, st));
+    int rc;
+    for (int s = T - 1; s >= 0; --s) {
+        rc = maavss_lstm_step_bwd(dy, gates, cells, w_hh_fwd, w_hh_rev, dgates, dcell, B, T, H, s, stream);
+        if (rc) return rc;
+    }
+    {
+        const long long n4 = 2LL * M * (H / 4);
+        int blocks = (int)((n4 + 255) / 256);
+        if (blocks > 148 * 8) blocks = 148 * 8;
+        lstm_hprev_kernel<<<blocks, 256, 0, st>>>(y, hprev, B, T, H / 4);
+        MAAVSS_LAUNCH_CHECK();
+    }
+    const float* w_ih[2] = {w_ih_fwd, w_ih_rev};
+    float* dw_ih[2] = {dw_ih_fwd, dw_ih_rev};
+    float* dw_hh[2] = {dw_hh_fwd, dw_hh_rev};
+    for (int d = 0; d < 2; ++d) {
+        const float* dg = dgates + (size_t)d * M * 4 * H;
+        if (dw_ih[d]) {
+            rc = proj_wgrad(dg, x, dw_ih[d], M, 4 * H, I, accumulate, gws, g, stream);
+            if (rc) return rc;
+        }
+        if (dw_hh[d]) {
+            rc = proj_wgrad(dg, hprev + (size_t)d * M * H, dw_hh[d], M, 4 * H, H, accumulate, gws, g, stream);
+            if (rc) return rc;
+        }
+        if (dx) {
+            // dx[M, I] (+)= dg[M, 4H] w_ih[4H, I]: the second direction accumulates into the first one's result
+            if (M >= 32 && maavss_gemm_tf32x3_supported(I, M, 4 * H, 1, I, 0, 4 * H, I, 1) && maavss_gemm_tf32x3_workspace_bytes(I, M, 4 * H) <= g) {
+                rc = maavss_gemm_tf32x3(w_ih[d], 1, I, dg, 0, 4 * H, I, M, 4 * H, dx, I, 1, nullptr, 0, MAAVSS_ACT_NONE, 0.f, d, gws, g, stream);
+            } else if (d == 0) {
+                rc = maavss_linear_dgrad(dg, w_ih[d], dx, M, 4 * H, I, stream);
+            } else {
+                float* part = (float*)((uint8_t*)hprev + al256(sizeof(float) * 2 * (size_t)M * H));
+                rc = maavss_linear_dgrad(dg, w_ih[d], part, M, 4 * H, I, stream);
+                if (!rc) rc = maavss_add_noise(dx, part, 1.0f, dx, (long long)M * I, stream);      // dx += part (unfused a + b * 1)
+            }
+            if (rc) return rc;
+        }
+    }
+    return MAAVSS_OK;
+}

@@ -209,7 +209,10 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32x3_kernel(const __grid_co
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        // The whole warp walks the loop (uniform control flow: descriptors and barrier waits live in uniform registers) and one
+        // elected lane issues.  Inside an `if (lane == 0)` region every tcgen05.mma paid vector -> uniform register moves for
+        // its descriptors: ~62 cycles per issue against the 33 the tensor pipe needs for a 128 x 64 x 8 tf32 MMA.
+        {
             const uint32_t idesc = tc::make_idesc(2, BM, BN) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16);
             // Descriptors are built once: the address field is the low 14 bits (units of 16 bytes) and every tile of the ring
             // stays below 256 KB, so a stage / k-step / lo-tile offset is a plain add.  The single issuing thread has to feed a
@@ -236,9 +239,9 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32x3_kernel(const __grid_co
                     for (int kb = kc; kb < kend; ++kb) {
                         tc::mbar_wait(&ready[s], ph);
                         tc::tc_fence_after();
-                        if (p.trace && blockIdx.x == 0 && tr_m < 48) p.trace[tr_m * 8 + 4] = clock64();
+                        if (p.trace && blockIdx.x == 0 && lane == 0 && tr_m < 48) p.trace[tr_m * 8 + 4] = clock64();
                         uint64_t ad = a_desc0 + (uint64_t)s * STG, bd = b_desc0 + (uint64_t)s * STG;
-                        if (!(p.dbg & 2)) {
+                        if (!(p.dbg & 2) && tc::elect_one()) {
 #pragma unroll
                             for (int k = 0; k < BK / 8; ++k) {
                                 tc::umma_tf32(d_tmem, ad + LO, bd, idesc, (kb != kc) || (k != 0));      // the two small terms first
@@ -248,11 +251,13 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32x3_kernel(const __grid_co
                                 bd += b_step;
                             }
                         }
-                        tc::umma_commit(&empty[s]);
-                        if (p.trace && blockIdx.x == 0 && tr_m < 48) p.trace[tr_m++ * 8 + 5] = clock64();
+                        __syncwarp();
+                        if (tc::elect_one()) tc::umma_commit(&empty[s]);
+                        if (p.trace && blockIdx.x == 0 && lane == 0 && tr_m < 48) p.trace[tr_m * 8 + 5] = clock64();
+                        ++tr_m;
                         if (++s == STAGES) { s = 0; ph ^= 1; }
                     }
-                    tc::umma_commit(&tfull[a]);
+                    if (tc::elect_one()) tc::umma_commit(&tfull[a]);
                 }
             }
         }

@@ -174,7 +174,11 @@ class ConvTransposeFn(torch.autograd.Function):
 
 def _allreduce_partial(partial):
     import torch.distributed as dist
-    dist.all_reduce(partial, group=SYNC_BN_GROUP)
+    from . import parallel
+    if parallel.native_comm() is not None and partial.is_cuda:
+        parallel.allreduce_sum_(partial)
+    else:
+        dist.all_reduce(partial, group=SYNC_BN_GROUP)
     return dist.get_world_size(SYNC_BN_GROUP)
 
 
@@ -404,7 +408,9 @@ class LinearActFn(torch.autograd.Function):
 
 
 class LSTMFn(torch.autograd.Function):
-    """nn.LSTM(bias=False, batch_first=True, bidirectional=True, num_layers=1): x (B, T, I) -> y (B, T, 2H)."""
+    """nn.LSTM(bias=False, batch_first=True, bidirectional=True, num_layers=1): x (B, T, I) -> y (B, T, 2H).
+    One C-ABI call per direction of autograd (maavss_bilstm_fwd / maavss_bilstm_bwd): projections, recurrent steps, the
+    h_{t-1} gather and every gradient product are enqueued by the library."""
 
     @staticmethod
     def forward(ctx, x, w_ih_f, w_hh_f, w_ih_r, w_hh_r):
@@ -414,50 +420,40 @@ class LSTMFn(torch.autograd.Function):
         L = lib()
         dev = x.device
         gin = torch.empty(2, B, T, 4 * H, device=dev, dtype=torch.float32)
-        x2 = x.reshape(B * T, I)
-        for d, w in enumerate((w_ih_f, w_ih_r)):
-            linear_fwd_into(x2, w, None, gin[d].view(B * T, 4 * H))
         gates = torch.empty_like(gin)
         cells = torch.empty(2, B, T, H, device=dev, dtype=torch.float32)
         y = torch.empty(B, T, 2 * H, device=dev, dtype=torch.float32)
-        for s in range(T):
-            check(L.maavss_lstm_step_fwd(fptr(gin), fptr(w_hh_f), fptr(w_hh_r), fptr(gates), fptr(cells), fptr(y), B, T, H, s,
-                                         stream_ptr()))
+        nbytes = L.maavss_bilstm_workspace_bytes(B, T, I, H, 0)
+        ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+        check(L.maavss_bilstm_fwd(fptr(x), fptr(w_ih_f), fptr(w_hh_f), fptr(w_ih_r), fptr(w_hh_r), fptr(gin), fptr(gates), fptr(cells),
+                                  fptr(y), B, T, I, H, dptr(ws), ctypes.c_longlong(nbytes), stream_ptr()))
         ctx.cfg = (B, T, I, H)
-        ctx.save_for_backward(x2, w_ih_f, w_hh_f, w_ih_r, w_hh_r, gates, cells, y)
+        ctx.save_for_backward(x, w_ih_f, w_hh_f, w_ih_r, w_hh_r, gates, cells, y)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x2, w_ih_f, w_hh_f, w_ih_r, w_hh_r, gates, cells, y = ctx.saved_tensors
+        x, w_ih_f, w_hh_f, w_ih_r, w_hh_r, gates, cells, y = ctx.saved_tensors
         B, T, I, H = ctx.cfg
         L = lib()
         dev = dy.device
         dy = dy.contiguous()
         dgates = torch.empty_like(gates)
-        dcell = torch.zeros(2, B, H, device=dev, dtype=torch.float32)
-        for s in range(T - 1, -1, -1):
-            check(L.maavss_lstm_step_bwd(fptr(dy), fptr(gates), fptr(cells), fptr(w_hh_f), fptr(w_hh_r), fptr(dgates), fptr(dcell),
-                                         B, T, H, s, stream_ptr()))
-        # h_{t-1} of each direction (zero at its first step), as (B*T, H)
-        hprev = torch.zeros(2, B, T, H, device=dev, dtype=torch.float32)
-        hprev[0, :, 1:] = y[:, :-1, :H]
-        hprev[1, :, :-1] = y[:, 1:, H:]
-        grads = [None] * 5
-        dx = None
-        for d, (w_ih, w_hh, i_ih, i_hh) in enumerate(((w_ih_f, w_hh_f, 1, 2), (w_ih_r, w_hh_r, 3, 4))):
-            dg = dgates[d].reshape(B * T, 4 * H)
-            t, acc, grads[i_ih] = _grad_slot(w_ih, ctx.needs_input_grad[i_ih])
-            if t is not None:
-                linear_wgrad_into(dg, x2, t, None, acc)
-            t, acc, grads[i_hh] = _grad_slot(w_hh, ctx.needs_input_grad[i_hh])
-            if t is not None:
-                linear_wgrad_into(dg, hprev[d].reshape(B * T, H), t, None, acc)
-            if ctx.needs_input_grad[0]:
-                part = torch.empty(B * T, I, device=dev, dtype=torch.float32)
-                linear_dgrad_into(dg, w_ih, part)
-                dx = part if dx is None else dx.add_(part)
-        grads[0] = dx.reshape(B, T, I) if dx is not None else None
+        slots = [_grad_slot(w, ctx.needs_input_grad[i + 1]) for i, w in enumerate((w_ih_f, w_hh_f, w_ih_r, w_hh_r))]
+        accs = {a for t, a, _ in slots if t is not None}
+        if len(accs) > 1:            # mixed accumulate flags (a caller dropped some .grad): fresh tensors for all, added below
+            slots = [(torch.empty_like(w), 0, "add") if t is not None else (None, 0, None)
+                     for (t, a, r), w in zip(slots, (w_ih_f, w_hh_f, w_ih_r, w_hh_r))]
+        acc = next(iter({a for t, a, _ in slots if t is not None}), 0)
+        dx = torch.empty(B, T, I, device=dev, dtype=torch.float32) if ctx.needs_input_grad[0] else None
+        nbytes = L.maavss_bilstm_workspace_bytes(B, T, I, H, 1)
+        ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+        check(L.maavss_bilstm_bwd(fptr(dy), fptr(x), fptr(w_ih_f), fptr(w_hh_f), fptr(w_ih_r), fptr(w_hh_r), fptr(gates), fptr(cells),
+                                  fptr(y), fptr(dgates), _opt(dx), *[_opt(t) for t, _, _ in slots], acc, B, T, I, H, dptr(ws),
+                                  ctypes.c_longlong(nbytes), stream_ptr()))
+        grads = [dx]
+        for (t, a, ret), w in zip(slots, (w_ih_f, w_hh_f, w_ih_r, w_hh_r)):
+            grads.append(t if isinstance(ret, str) or ret is not None else None)
         return tuple(grads)
 
 

@@ -19,6 +19,7 @@ from . import nn_ops
 
 _GROUP = None
 _WORLD = 1
+_COMM = None        # maavss_comm* (ctypes.c_void_p): the library's own NCCL communicator (csrc/comm.cu)
 
 
 def init(backend=None, sync_bn=True):
@@ -37,7 +38,46 @@ def init(backend=None, sync_bn=True):
     _WORLD = world
     _GROUP = dist.group.WORLD if world > 1 else None
     nn_ops.SYNC_BN_GROUP = _GROUP if (sync_bn and world > 1) else None
+    if world > 1 and dist.get_backend() == "nccl" and os.environ.get("MAAVSS_TORCH_COLLECTIVES") != "1":
+        _init_native_comm(rank, world)
     return rank, world
+
+
+def _init_native_comm(rank, world):
+    """The hot-path collectives (gradient arena, BatchNorm partial sums, phasegram maxima) go through the library's C ABI
+    (maavss_comm_init / maavss_grad_allreduce / ...); torch.distributed only carries the 128-byte ncclUniqueId to the ranks
+    and stays the fallback (MAAVSS_TORCH_COLLECTIVES=1, and the gloo backend of the CPU tests)."""
+    global _COMM
+    import ctypes
+    from ._lib import check, lib
+    L = lib()
+    ident = (ctypes.c_ubyte * 128)()
+    if rank == 0:
+        check(L.maavss_comm_unique_id(ident))
+    t = torch.tensor(list(ident), dtype=torch.uint8, device="cuda")
+    dist.broadcast(t, src=0)
+    ident = (ctypes.c_ubyte * 128)(*t.cpu().tolist())
+    comm = ctypes.c_void_p()
+    check(L.maavss_comm_init(ctypes.byref(comm), rank, world, ident))
+    _COMM = comm
+
+
+def native_comm():
+    return _COMM
+
+
+def allreduce_sum_(t):
+    """In-place sum over ranks on the current stream (fp32 gradient slices, fp64 BatchNorm partial sums)."""
+    if _GROUP is None:
+        return t
+    if _COMM is not None and t.is_cuda and t.is_contiguous() and t.dtype in (torch.float32, torch.float64):
+        import ctypes
+        from ._lib import check, lib, stream_ptr
+        fn = lib().maavss_grad_allreduce if t.dtype == torch.float32 else lib().maavss_allreduce_sum_f64
+        check(fn(_COMM, ctypes.c_void_p(t.data_ptr()), t.numel(), stream_ptr()))
+        return t
+    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=_GROUP)
+    return t
 
 
 def world_size():
@@ -83,7 +123,7 @@ def allreduce_gradients(optimizer):
     """Sum the flat gradient arena over ranks; the 1/W average is folded into the Adam kernel (grad_scale)."""
     if _GROUP is None:
         return
-    dist.all_reduce(optimizer.flat.grad, op=dist.ReduceOp.SUM, group=_GROUP)
+    allreduce_sum_(optimizer.flat.grad)
     optimizer.grad_scale = 1.0 / _WORLD
 
 
@@ -107,7 +147,7 @@ class EarlyGradAllReduce:
         self.started = True
         self.side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(self.side):
-            dist.all_reduce(self.opt.flat.grad[self.offset:], op=dist.ReduceOp.SUM, group=_GROUP)
+            allreduce_sum_(self.opt.flat.grad[self.offset:])
 
     def finish(self):
         if _GROUP is None:
@@ -115,15 +155,22 @@ class EarlyGradAllReduce:
         g = self.opt.flat.grad
         if self.started:
             if self.offset > 0:
-                dist.all_reduce(g[:self.offset], op=dist.ReduceOp.SUM, group=_GROUP)
+                allreduce_sum_(g[:self.offset])
             torch.cuda.current_stream().wait_stream(self.side)
         else:
-            dist.all_reduce(g, op=dist.ReduceOp.SUM, group=_GROUP)
+            allreduce_sum_(g)
         self.started = False
         self.opt.grad_scale = 1.0 / _WORLD
 
 
 def allreduce_max_(t):
-    if _GROUP is not None:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=_GROUP)
+    """In-place MAX over ranks; int32 / uint32 words (float bits of non-negative values) go through the C ABI."""
+    if _GROUP is None:
+        return t
+    if _COMM is not None and t.is_cuda and t.is_contiguous() and t.dtype == torch.int32:
+        import ctypes
+        from ._lib import check, lib, stream_ptr
+        check(lib().maavss_allreduce_max_u32(_COMM, ctypes.c_void_p(t.data_ptr()), t.numel(), stream_ptr()))
+        return t
+    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=_GROUP)
     return t

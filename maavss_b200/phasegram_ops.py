@@ -54,8 +54,8 @@ def video_phasegram_windows(frames, num_windows, window_frames, resize=(64, 64),
                                     bstride, int(bool(cumulative)), stream_ptr()))
     check(L.maavss_phasegram_windows_max(fptr(pflat), dptr(mx), B, Tc, Tw, G, R, roll, int(bool(diff)), stream_ptr()))
     if max_group is not None and normalize:
-        import torch.distributed as dist
-        dist.all_reduce(mx, op=dist.ReduceOp.MAX, group=max_group)      # non-negative float bits order like integers
+        from . import parallel
+        parallel.allreduce_max_(mx)                                      # non-negative float bits order like integers
     check(L.maavss_phasegram_windows_write(fptr(pflat), dptr(mx), fptr(out), B, Tc, Tw, G, R, roll, int(bool(diff)),
                                            int(bool(normalize)), stream_ptr()))
     return out.unsqueeze(1)

@@ -78,4 +78,5 @@ class VideoAttention:
     def clip_attention(self, frames, attn_diff=False, clips=1):
         """The dataset's per-clip post-processing fused on the device (av_dataset.py:320-328): attention maps, optional
         temporal frame difference with a zero first frame, division by the clip's (signed) maximum."""
-        return attn_ops.diff_normalise(self.inference_device(frames), attn_diff, clips=clips)
+        f = frames.to(self.device, torch.float32, non_blocking=True)
+        return self.model.attention_maps(f, post=2 if attn_diff else 1, clips=clips)

@@ -79,24 +79,66 @@ class ViTPlan:
                 ln2=(sd[p + "norm2.weight"], sd[p + "norm2.bias"]), w_fc1=_bf16(sd[p + "mlp.fc1.weight"]), b_fc1=sd[p + "mlp.fc1.bias"],
                 w_fc2=_bf16(sd[p + "mlp.fc2.weight"]), b_fc2=sd[p + "mlp.fc2.bias"]))
         self._pos_cache = {}
+        self._native = self._create_native(sd)
+        self._prepared = set()
+
+    # ---- the one-call C-ABI plan (maavss_vit_create / maavss_vit_attn_maps, csrc/vit_plan.cu) ----
+    _BLOCK_KEYS = ("norm1.weight", "norm1.bias", "attn.qkv.weight", "attn.qkv.bias", "attn.proj.weight", "attn.proj.bias",
+                   "norm2.weight", "norm2.bias", "mlp.fc1.weight", "mlp.fc1.bias", "mlp.fc2.weight", "mlp.fc2.bias")
+
+    def _create_native(self, sd):
+        import ctypes
+        n0 = sd["pos_embed"].shape[1] - 1
+        grid = int(round(math.sqrt(n0)))
+        if grid * grid != n0:
+            raise ValueError("pos_embed is not a square grid")
+        zeros3 = torch.zeros(3 * self.dim, device=self.device)
+        ptrs = []
+        keep = [zeros3]
+        for i in range(self.depth):
+            for k in self._BLOCK_KEYS:
+                t = sd.get(f"blocks.{i}.{k}")
+                if t is None and k == "attn.qkv.bias":
+                    t = zeros3                                   # qkv_bias=False models
+                keep.append(t)
+                ptrs.append(t.data_ptr())
+        arr = (ctypes.c_void_p * len(ptrs))(*ptrs)
+        plan = ctypes.c_void_p()
+        pw = sd["patch_embed.proj.weight"].reshape(self.dim, -1).contiguous()
+        torch.cuda.synchronize(self.device)
+        check(lib().maavss_vit_create(ctypes.byref(plan), self.dim, self.depth, self.patch, sd["patch_embed.proj.weight"].shape[1], grid,
+                                      fptr(sd["cls_token"].reshape(-1).contiguous()), fptr(sd["pos_embed"].reshape(-1, self.dim).contiguous()),
+                                      fptr(pw), fptr(sd["patch_embed.proj.bias"]), arr))
+        del keep
+        return plan
+
+    def __del__(self):
+        try:
+            if getattr(self, "_native", None):
+                lib().maavss_vit_destroy(self._native)
+                self._native = None
+        except Exception:
+            pass
+
+    def native_pos_embed(self, H, W):
+        """The plan's interpolated position embedding for an (H, W) input (tests: equals interpolate_pos_encoding)."""
+        self._prepare(H, W)
+        gh, gw = H // self.patch, W // self.patch
+        out = torch.empty(1 + gh * gw, self.dim, device=self.device)
+        check(lib().maavss_vit_pos_embed(self._native, H, W, fptr(out)))
+        return out
+
+    def _prepare(self, H, W):
+        if (H, W) not in self._prepared:
+            check(lib().maavss_vit_prepare(self._native, H, W))
+            self._prepared.add((H, W))
 
     def pos_embed_for(self, w, h):
-        """interpolate_pos_encoding (dino/vision_transformer.py:174-194), evaluated once per input size."""
+        """interpolate_pos_encoding (dino/vision_transformer.py:174-194) for a (w, h) = (rows, columns) input, evaluated once
+        per size by the plan's bicubic kernel."""
         key = (w, h)
         if key not in self._pos_cache:
-            pos = self.pos
-            n0 = pos.shape[1] - 1
-            npatch = (w // self.patch) * (h // self.patch)
-            if npatch == n0 and w == h:
-                out = pos[0]
-            else:
-                w0, h0 = w // self.patch + 0.1, h // self.patch + 0.1
-                s = int(math.sqrt(n0))
-                pp = F.interpolate(pos[:, 1:].reshape(1, s, s, self.dim).permute(0, 3, 1, 2),
-                                   scale_factor=(w0 / math.sqrt(n0), h0 / math.sqrt(n0)), mode="bicubic")
-                assert int(w0) == pp.shape[-2] and int(h0) == pp.shape[-1]
-                out = torch.cat((pos[0, :1], pp.permute(0, 2, 3, 1).reshape(-1, self.dim)), 0)
-            self._pos_cache[key] = out.contiguous()
+            self._pos_cache[key] = self.native_pos_embed(w, h)
         return self._pos_cache[key]
 
     @torch.no_grad()
@@ -133,8 +175,25 @@ class ViTPlan:
         return rows, gh, gw
 
     @torch.no_grad()
-    def attention_maps(self, frames):
-        """VideoAttention._inference on the device: (T, 3, H, W) -> (T, 1, gh*P, gw*P), per-frame max-normalised."""
+    def attention_maps(self, frames, post=0, clips=1):
+        """VideoAttention._inference on the device in ONE C-ABI call: (T, 3, H, W) -> (T, 1, gh*P, gw*P), per-frame
+        max-normalised (post 0); post 1 / 2 adds the dataset's clip normalise / frame difference + clip normalise
+        (av_dataset.py:323-328) over `clips` equal groups of frames."""
+        import ctypes
+        frames = frames.contiguous()
+        T, C, H, W = frames.shape
+        self._prepare(H, W)
+        gh, gw = H // self.patch, W // self.patch
+        out = torch.empty(T, 1, gh * self.patch, gw * self.patch, device=frames.device, dtype=torch.float32)
+        nbytes = lib().maavss_vit_workspace_bytes(self._native, T, H, W, clips)
+        ws = torch.empty(nbytes, device=frames.device, dtype=torch.uint8)
+        check(lib().maavss_vit_attn_maps(self._native, fptr(frames), T, H, W, fptr(out), int(post), int(clips), dptr(ws),
+                                         ctypes.c_longlong(nbytes), stream_ptr()))
+        return out
+
+    @torch.no_grad()
+    def attention_maps_composed(self, frames):
+        """The same result composed call by call from Python (kept for tests of the individual entry points)."""
         rows, gh, gw = self.cls_attention_rows(frames)
         T, heads, N = rows.shape
         out = torch.empty(T, 1, gh * self.patch, gw * self.patch, device=frames.device, dtype=torch.float32)

@@ -122,3 +122,26 @@ def test_video_attention_class_golden(golden):
     # crop to a multiple of the patch size (video_attention.py:43-47)
     odd = va._inference(synth.frames(1, 70, 77, seed=5))
     assert odd.shape == (1, 1, 64, 72)
+
+
+def test_vit_native_plan_matches_composed_and_torch():
+    """The one-call C-ABI extractor (maavss_vit_create / _prepare / _attn_maps, csrc/vit_plan.cu): identical to the
+    call-by-call composition, its bicubic position-embedding resize equals torch's interpolate_pos_encoding arithmetic
+    (dino/vision_transformer.py:174-194), and the fused post-processing equals attn_ops.diff_normalise."""
+    from maavss_b200 import attn_ops, vit_ops
+    from oracle import vit as ov
+    sd = synth.vit_state_dict(depth=2)
+    plan = vit_ops.ViTPlan(sd, torch.device("cuda"))
+    for H, W in ((256, 256), (64, 72), (224, 224)):
+        ref = ov.pos_embed_for(sd, H, W)[0]
+        got = plan.native_pos_embed(H, W).cpu()
+        assert got.shape == ref.shape
+        assert float((got - ref).abs().max()) < 2e-6 * float(ref.abs().max()) + 1e-7, (H, W)
+    fr = synth.frames(6, 64, 72, seed=21).cuda()
+    one = plan.attention_maps(fr)
+    two = plan.attention_maps_composed(fr)
+    assert torch.equal(one, two)
+    for post, diff in ((1, False), (2, True)):
+        fused = plan.attention_maps(fr, post=post, clips=2)
+        sep = attn_ops.diff_normalise(two, diff, clips=2)
+        assert torch.equal(fused, sep)
