@@ -16,6 +16,7 @@ Sub-records on the same line, each with its own clock sample and >= 20 timed ite
     "vit"     configs[2]: frame-diff + DINO ViT-S/8 attention maps over a 64-frame clip           (video_attention.py:38-103)   [N = 1]
     "stft"    configs[4]: STFT / iSTFT bandwidth sweep, n_fft 512-4096 x hop n/8,n/4,n/2 (+256/66), 1024 x 10 s clips           [N = 1]
     "torch_eager_b200"    the same two train steps through PyTorch eager (cuDNN / cuBLAS, TF32 off) on the same GPU            [N = 1]
+    "pipeline"            the headline step fed from RAW inputs: audio memmap + uint8 frames -> H2D -> ViT -> STFT -> train step      [N = 1]
     "cpu_baseline"        the oracle port of the headline step on the box's host cores                                          [N = 1]
 
     python bench.py --gpus N --steps K --warmup W            our arm  (torchrun for N > 1, weak scaling: 16 clips / GPU)
@@ -458,6 +459,61 @@ def leg_torch_eager(ctx):
     return out
 
 
+def leg_pipeline(ctx, steps):
+    """The train.py loop END TO END from raw inputs (reference: Dataset.__getitem__ with num_workers=0 inside
+    the training process, av_dataset.py:302-342,365-377): per step, 16 clips are sliced out of the float32 audio memmap and their
+    12 decoded uint8 frames gathered on the host, copied to the device, normalised, pushed through the DINO ViT-S/8 extractor
+    (192 frames, frame difference + clip normalise fused), STFT'd, and trained on (4 windows + Adam) -- the batch of step i+1
+    staged on side streams while step i trains.  Host gather, H2D, front end and the D2H of the losses are all inside the timed
+    region."""
+    import tempfile
+    torch = ctx.torch
+    import numpy as np
+    from maavss_b200 import av_dataset, avse_model, input_pipeline, optim, train_step, video_attention
+    B = B_PER_GPU
+    n = HOPS_PER_FRAME * HOP * CLIP_FRAMES
+    tmp = tempfile.mkdtemp(prefix="maavss_bench_")
+    g = torch.Generator().manual_seed(99)
+    input_pipeline.save_audio_memmap(tmp, [(torch.randn(40 * n, generator=g) * 0.1).numpy() for _ in range(4)])
+    amap = input_pipeline.AudioMemmap(tmp)
+    videos = [torch.randint(0, 256, (CLIP_FRAMES, FRAME, FRAME, 3), generator=g, dtype=torch.uint8).numpy() for _ in range(2 * B)]
+    va = video_attention.VideoAttention(state_dict=video_attention.random_state_dict(seed=0))
+    ds = av_dataset.AV_Dataset(num_frames=CLIP_FRAMES, frame_hop=2, fft_len=N_FFT, hops_per_frame=HOPS_PER_FRAME, noise_std=NOISE_STD,
+                               framerate=FPS, samplerate=SR, attention_extractor=va)
+    torch.manual_seed(0)
+    model = avse_model.AV_Fusion_Model([B, 2, 64, 128], [B, 1, 8, 4096], 8)
+    model.train()
+    opt = optim.Adam(model.parameters(), lr=LR)
+    step = train_step.FusionTrainStep(model, opt, num_seq=NUM_SEQ, num_frames=NUM_FRAMES, hops_per_frame=HOPS_PER_FRAME, p_size=64,
+                                      loss_coeff=LOSS_COEFF, graph=not ctx.args.eager)
+    pipe = input_pipeline.ClipBatchPipeline(ds, amap, lambda i: videos[i], va, device=ctx.dev)
+    locs = lambda i: [((i + b) % 4, (3 * i + b) % 30) for b in range(B)]
+    idxs = lambda i: [(i * B + b) % (2 * B) for b in range(B)]
+    losses = []
+
+    def one(i):
+        pipe.submit(locs(i + 1), idxs(i + 1))
+        x, y, attn, _ = pipe.get()
+        out = step(x, y, attn)
+        losses.append(torch.stack(out).cpu())
+
+    pipe.submit(locs(0), idxs(0))
+    for i in range(3):
+        one(i)
+    clocks = ClockSampler(ctx.local).start()
+    ms = timed_steps(ctx, lambda i: one(i + 3), steps) / steps
+    clk = clocks.stop()
+    rec = {"metric": "train clips/sec from raw inputs (audio memmap + decoded uint8 frames -> ViT -> train step)", "value": round(B / ms * 1e3, 1),
+           "unit": "clips/s", "ms_per_step": round(ms, 3), "steps": steps, "clips_per_step": B, "frames_through_vit_per_step": B * CLIP_FRAMES,
+           "h2d_bytes_per_step": B * (4 * n + CLIP_FRAMES * FRAME * FRAME * 3), "d2h_bytes_per_step": 12, "final_loss": float(losses[-1][0]),
+           "vit": "ViT-S/8 depth 12, random dino init, bf16 tcgen05", "clocks": clk,
+           "input_pipeline": "input_pipeline.ClipBatchPipeline: host gather + H2D + front end of step i+1 on side streams while step i trains"}
+    step._graph = None
+    del step, model, opt, pipe, va
+    torch.cuda.empty_cache()
+    return rec
+
+
 def safe(ctx, name, fn, *a):
     try:
         if ctx.args.verbose:
@@ -642,6 +698,8 @@ def run_ours(args):
             line["vit"] = safe(ctx, "vit", leg_vit, 20)
         if not args.no_stft:
             line["stft"] = safe(ctx, "stft", leg_stft, 20)
+        if not args.no_pipeline:
+            line["pipeline"] = safe(ctx, "pipeline", leg_pipeline, 20)
         if not args.no_torch:
             line["torch_eager_b200"] = safe(ctx, "torch_eager", leg_torch_eager)
         if not args.no_cpu:
@@ -673,13 +731,14 @@ def main():
     ap.add_argument("--no-vit", action="store_true", help="skip the configs[2] leg")
     ap.add_argument("--no-stft", action="store_true", help="skip the configs[4] leg")
     ap.add_argument("--no-torch", action="store_true", help="skip the PyTorch-eager-on-B200 leg")
+    ap.add_argument("--no-pipeline", action="store_true", help="skip the raw-inputs-to-step pipeline leg")
     ap.add_argument("--only-headline", action="store_true", help="headline + roofline only (profiling runs)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--verbose", action="store_true", help="progress notes on stderr")
     ap.add_argument("--breakdown", default=None, help="write the full per-call breakdown of the eager profiling steps to this file")
     args = ap.parse_args()
     if args.only_headline:
-        args.no_cpu = args.no_frames = args.no_vit = args.no_stft = args.no_torch = True
+        args.no_cpu = args.no_frames = args.no_vit = args.no_stft = args.no_torch = args.no_pipeline = True
     if args.warmup < 3:
         args.warmup = 3
     if args.impl == "reference":

@@ -280,6 +280,12 @@ int maavss_f32_to_bf16(const float* in, void* out_bf16, long long n, void* strea
 int maavss_vit_cls_attn_row(const float* q, long long ldq, const float* k, long long ldk, float* out, int T, int heads, int N,
                             float scale, void* stream);
 
+/* Decoded clip frames (frames, H, W, 3) uint8 -> (frames, 3, H, W) fp32 = (x / 255 - mean[c]) / std[c]: the permute, /255. and
+ * Normalize of gen_av_example (av_dataset.py:108-112,312-317), bit-identical to the torch expression.  mean / std: 3 HOST
+ * floats each.  (RandomResizedCrop is a random augmentation and stays with the caller.) */
+int maavss_frames_u8_normalize(const unsigned char* frames_hwc, float* out_chw, long long frames, int H, int W,
+                               const float* mean3_host, const float* std3_host, void* stream);
+
 /* ---- the whole extractor as one call: VideoAttention.__load_model / _inference (video_attention.py:38-160).
  * vit_create copies the weights into a plan (GEMM weights as bf16).  All pointers are DEVICE fp32 tensors in dino's
  * state_dict layout: cls_token (dim), pos_embed (1 + pos_grid^2, dim), patch_embed.proj.weight (dim, in_chans*patch*patch),

@@ -39,7 +39,37 @@ __global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ x
     out[c] = accumulate ? out[c] + s : s;
 }
 
+// Decoded video frames (T, H, W, 3) uint8 -> network input (T, 3, H, W) fp32: x / 255, then (x - mean[c]) / std[c]
+// (av_dataset.py:312-317: permute, /255., Normalize).  One thread per pixel reads its 3 interleaved bytes and writes the three
+// planes (coalesced fp32 stores; the byte loads of a warp cover 96 contiguous bytes).  Unfused division and subtraction so
+// that the result is bit-identical to the torch expression (video / 255. - mean) / std.
+__global__ void __launch_bounds__(256) frames_u8_kernel(const unsigned char* __restrict__ in, float* __restrict__ out, long long frames,
+                                                        long long hw, float m0, float m1, float m2, float s0, float s1, float s2) {
+    const long long n = frames * hw;
+    for (long long p = (long long)blockIdx.x * 256 + threadIdx.x; p < n; p += (long long)gridDim.x * 256) {
+        const long long f = p / hw, q = p - f * hw;
+        const unsigned char* src = in + p * 3;
+        float* dst = out + f * 3 * hw + q;
+        dst[0] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)src[0], 255.f), m0), s0);
+        dst[hw] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)src[1], 255.f), m1), s1);
+        dst[2 * hw] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)src[2], 255.f), m2), s2);
+    }
+}
+
 }  // namespace
+
+extern "C" int maavss_frames_u8_normalize(const unsigned char* frames_hwc, float* out_chw, long long frames, int H, int W,
+                                          const float* mean3_host, const float* std3_host, void* stream) {
+    if (frames == 0) return MAAVSS_OK;
+    MAAVSS_CHECK_ARG(frames_hwc && out_chw && mean3_host && std3_host && H > 0 && W > 0, "frames_u8_normalize: bad argument");
+    const long long n = frames * H * W;
+    int blocks = (int)((n + 255) / 256);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    frames_u8_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(frames_hwc, out_chw, frames, (long long)H * W, mean3_host[0], mean3_host[1],
+                                                                mean3_host[2], std3_host[0], std3_host[1], std3_host[2]);
+    MAAVSS_LAUNCH_CHECK();
+    return MAAVSS_OK;
+}
 
 extern "C" int maavss_colsum(const float* x, int rows, long long cols, float* out, int accumulate, void* stream) {
     if (cols == 0) return MAAVSS_OK;

@@ -180,8 +180,8 @@ extern "C" int maavss_vit_prepare(maavss_vit_plan* p, int H, int W) {
     } else {
         // dino adds 0.1 to the target grid "to avoid floating point error in the interpolation" (:186-190); torch's
         // scale_factor path maps destination to source coordinates with 1 / scale_factor
-        const float sy = (float)(((double)gh + 0.1) / (double)p->pos_grid), sx = (float)(((double)gw + 0.1) / (double)p->pos_grid);
-        pos_bicubic_kernel<<<gh * gw, 128>>>(p->pos + D, data + D, p->pos_grid, gh, gw, p->dim, 1.0f / sy, 1.0f / sx);
+        const float inv_sy = (float)((double)p->pos_grid / ((double)gh + 0.1)), inv_sx = (float)((double)p->pos_grid / ((double)gw + 0.1));
+        pos_bicubic_kernel<<<gh * gw, 128>>>(p->pos + D, data + D, p->pos_grid, gh, gw, p->dim, inv_sy, inv_sx);
         MAAVSS_LAUNCH_CHECK();
         MAAVSS_CUDA(cudaStreamSynchronize(nullptr));
     }

@@ -136,7 +136,7 @@ def test_vit_native_plan_matches_composed_and_torch():
         ref = ov.pos_embed_for(sd, H, W)[0]
         got = plan.native_pos_embed(H, W).cpu()
         assert got.shape == ref.shape
-        assert float((got - ref).abs().max()) < 2e-6 * float(ref.abs().max()) + 1e-7, (H, W)
+        assert float((got - ref).abs().max()) < 4e-6 * float(ref.abs().max()) + 1e-7, (H, W, float((got - ref).abs().max()))
     fr = synth.frames(6, 64, 72, seed=21).cuda()
     one = plan.attention_maps(fr)
     two = plan.attention_maps_composed(fr)
