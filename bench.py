@@ -514,6 +514,35 @@ def leg_pipeline(ctx, steps):
     return rec
 
 
+def leg_flow(ctx, iters):
+    """flow.py's loop body (Shi-Tomasi corners + 3-level pyramidal LK, flow.py:11-20,28,37) on 256 x 256 synthetic frame pairs,
+    beside OpenCV -- the arithmetic the reference itself calls -- on one host core."""
+    torch = ctx.torch
+    import synth
+    from maavss_b200 import flow
+    pairs = [synth.flow_frames(100 + i) for i in range(8)]
+    dev_pairs = [(torch.from_numpy(a).to(ctx.dev), torch.from_numpy(b).to(ctx.dev)) for a, b in pairs]
+    fn = lambda i: flow.track(*dev_pairs[i % 8])
+    for i in range(3):
+        fn(i)
+    ms = timed_steps(ctx, fn, iters) / iters
+    rec = {"metric": "sparse optical flow frame pairs/sec (goodFeaturesToTrack + calcOpticalFlowPyrLK, flow.py parameters)",
+           "value": round(1e3 / ms, 1), "unit": "pairs/s", "ms_per_pair": round(ms, 4), "frame": "256x256 uint8", "iters": iters,
+           "note": "latency bound: ~10 small launches and one 4-byte D2H (corner count) per pair"}
+    try:
+        import cv2
+        cv2.setNumThreads(1)
+        t0 = time.perf_counter()
+        for i in range(iters):
+            a, b = pairs[i % 8]
+            p0 = cv2.goodFeaturesToTrack(a, mask=None, maxCorners=100, qualityLevel=0.3, minDistance=7, blockSize=7)
+            cv2.calcOpticalFlowPyrLK(a, b, p0, None, winSize=(15, 15), maxLevel=2, criteria=(3, 10, 0.03))
+        rec["opencv_cpu_1_thread_pairs_per_s"] = round(iters / (time.perf_counter() - t0), 1)
+    except ImportError:
+        pass
+    return rec
+
+
 def safe(ctx, name, fn, *a):
     try:
         if ctx.args.verbose:
@@ -700,6 +729,7 @@ def run_ours(args):
             line["stft"] = safe(ctx, "stft", leg_stft, 20)
         if not args.no_pipeline:
             line["pipeline"] = safe(ctx, "pipeline", leg_pipeline, 20)
+            line["flow"] = safe(ctx, "flow", leg_flow, 40)
         if not args.no_torch:
             line["torch_eager_b200"] = safe(ctx, "torch_eager", leg_torch_eager)
         if not args.no_cpu:

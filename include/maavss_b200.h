@@ -360,6 +360,26 @@ int maavss_phasegram_windows_max(const float* pflat, void* max_ws, int B, int Tc
 int maavss_phasegram_windows_write(const float* pflat, const void* max_ws, float* out, int B, int Tc, int Tw, int G, int R,
                                    int batch_roll, int diff, int normalize, void* stream);
 
+/* ------------------------------------------------------------- sparse optical flow (flow.py) ---------- */
+/* flow.py:26 cv2.cvtColor(frame, COLOR_BGR2GRAY) for uint8 frames: (B*3735 + G*19235 + R*9798 + 2^14) >> 15 (OpenCV 4.x). */
+int maavss_bgr_to_gray(const unsigned char* bgr, unsigned char* gray, long long pixels, void* stream);
+/* flow.py:11-14,28 cv2.goodFeaturesToTrack(gray, maxCorners, qualityLevel, minDistance, blockSize) (Shi-Tomasi: minimum
+ * eigenvalue of the block_size x block_size gradient covariance, Sobel 3; threshold at quality * max; 3x3 non-maximum
+ * suppression; strongest first with a minimum mutual distance).  gray (H, W) uint8 -> corners_xy (max_corners, 2) = (x, y)
+ * floats in OpenCV's order, *count (device int) = how many.  workspace: maavss_flow_features_workspace_bytes(H, W). */
+long long maavss_flow_features_workspace_bytes(int H, int W);
+int maavss_flow_good_features(const unsigned char* gray, int H, int W, int max_corners, float quality_level, float min_distance,
+                              int block_size, float* corners_xy, int* count, void* workspace, long long workspace_bytes, void* stream);
+/* flow.py:17-19,37 cv2.calcOpticalFlowPyrLK(prev, next, p0, None, winSize=(win, win), maxLevel, criteria=(EPS|COUNT, max_iter,
+ * epsilon)): pyramids by pyrDown, Scharr derivatives, the 14-bit fixed-point bilinear windows and the iteration rules of
+ * OpenCV's LKTrackerInvoker.  prev_pts / next_pts (max_points, 2) device floats (x, y); count: optional DEVICE int (points
+ * beyond it are skipped; NULL = all max_points); status (max_points) 1 = tracked; err (max_points, may be NULL) = mean |J - I| / 32
+ * over the window.  min_eig_threshold: OpenCV's default is 1e-4.  workspace: maavss_flow_lk_workspace_bytes(H, W, max_level). */
+long long maavss_flow_lk_workspace_bytes(int H, int W, int max_level);
+int maavss_flow_pyr_lk(const unsigned char* prev_gray, const unsigned char* next_gray, int H, int W, const float* prev_pts, int max_points,
+                       const int* count, float* next_pts, unsigned char* status, float* err, int win, int max_level, int max_iter,
+                       float epsilon, float min_eig_threshold, void* workspace, long long workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------- data parallel ---------- */
 /* One NCCL communicator over the GPUs of the box (one process per GPU).  Rank 0 calls comm_unique_id (128 bytes) and hands
  * the bytes to every rank (any side channel: torch.distributed store, MPI, a file); every rank then calls comm_init with its

@@ -25,7 +25,7 @@ REF = "/root/reference"
 
 
 def install_shim():
-    for name in ["torchsummary", "matplotlib", "matplotlib.pyplot", "wandb", "cv2"]:
+    for name in ["torchsummary", "matplotlib", "matplotlib.pyplot", "wandb"] + ([] if "flow" in sys.argv else ["cv2"]):
         if name not in sys.modules:
             sys.modules[name] = types.ModuleType(name)
     sys.modules["torchsummary"].summary = lambda *a, **k: None
@@ -181,6 +181,23 @@ def golden_attn_cache():
     jpg = torch.stack(jpg).reshape(2, 4, 64, 64)
     save("attn_cache", u8=u8, totensor=back, jpeg_max_err=float((jpg - maps.clamp(0, 1)).abs().max()),
          raw_max_err=float((back - maps.clamp(0, 1)).abs().max()))
+
+
+def golden_flow():
+    """cv2 (the arithmetic flow.py calls) on seeded synthetic frame pairs: corners, tracked points, status, error."""
+    import cv2
+    out = {}
+    for seed in (1, 2, 3):
+        a, b = synth.flow_frames(seed)
+        p0 = cv2.goodFeaturesToTrack(a, mask=None, maxCorners=100, qualityLevel=0.3, minDistance=7, blockSize=7)       # flow.py:11-14,28
+        p1, st, err = cv2.calcOpticalFlowPyrLK(a, b, p0, None, winSize=(15, 15), maxLevel=2,
+                                               criteria=(cv2.TERM_CRITERIA_EPS | cv2.TERM_CRITERIA_COUNT, 10, 0.03))   # flow.py:17-19,37
+        dense = cv2.goodFeaturesToTrack(a, mask=None, maxCorners=100, qualityLevel=0.01, minDistance=7, blockSize=7)
+        out.update({f"s{seed}_p0": p0, f"s{seed}_p1": p1, f"s{seed}_st": st, f"s{seed}_err": err, f"s{seed}_dense": dense,
+                    f"s{seed}_eig_max": np.float32(cv2.cornerMinEigenVal(a, 7, ksize=3).max())})
+    rgb = np.random.RandomState(5).randint(0, 256, (32, 40, 3), dtype=np.uint8)
+    out["gray"] = cv2.cvtColor(rgb, cv2.COLOR_BGR2GRAY)
+    save("flow", **out)
 
 
 def run_model_case(name, model, x_a, x_v, y_a, y_v, loss_coeff=0.001):

@@ -123,3 +123,27 @@ def param_digest(model):
     return np.stack(out)
 
 
+
+
+def flow_frames(seed, H=256, W=256, shift=(1.7, -2.3)):
+    """A textured gray frame with a few rectangles (strong corners) and the same scene translated by `shift` = (dx, dy) pixels
+    (bilinear resampling) plus a slow brightness ramp: uint8 (H, W) x 2, as numpy arrays."""
+    g = gen(seed)
+    base = torch.rand(1, 1, H // 8 + 4, W // 8 + 4, generator=g)
+    big = torch.nn.functional.interpolate(base, size=(H + 32, W + 32), mode="bicubic", align_corners=False)[0, 0]
+    big = (big - big.min()) / (big.max() - big.min()) * 200.0 + 20.0
+    rs = np.random.RandomState(seed)
+    for _ in range(14):
+        y, x = rs.randint(20, H - 20), rs.randint(20, W - 20)
+        h, w = rs.randint(8, 30), rs.randint(8, 30)
+        big[y:y + h, x:x + w] = float(rs.randint(0, 256))
+    yy, xx = torch.meshgrid(torch.arange(H, dtype=torch.float32), torch.arange(W, dtype=torch.float32), indexing="ij")
+
+    def sample(dx, dy):
+        gx = (xx + 16 - dx) / (W + 32 - 1) * 2 - 1
+        gy = (yy + 16 - dy) / (H + 32 - 1) * 2 - 1
+        grid = torch.stack((gx, gy), -1)[None]
+        return torch.nn.functional.grid_sample(big[None, None], grid, mode="bilinear", align_corners=True)[0, 0]
+    a = sample(0.0, 0.0).round().clamp(0, 255).to(torch.uint8).numpy()
+    b = (sample(*shift) * 1.02 + 1.0).round().clamp(0, 255).to(torch.uint8).numpy()
+    return a, b

@@ -182,3 +182,24 @@ def test_attn_cache_quantiser(golden):
     out = oc.load_clips(u8, True)
     assert out.shape == (2, 4, 64, 64) and float(out[:, 0].abs().max()) == 0.0
     assert float(out.amax(dim=(1, 2, 3)).min()) == pytest.approx(1.0, abs=1e-6)
+
+
+def test_flow_corner_restatement_matches_cv2_goldens(golden):
+    """oracle/flow.py's numpy restatement of cv2.goodFeaturesToTrack (Shi-Tomasi, flow.py:11-14,28) against the cv2 outputs in
+    tests/golden/flow.npz: identical corner lists (coordinates AND order) at the reference's quality 0.3 and at 0.01, where the
+    100-corner cap and the minimum-distance rule decide; and against cv2 itself when it is importable."""
+    from oracle import flow as of
+    g = golden("flow")
+    for seed in (1, 2, 3):
+        a, b = synth.flow_frames(seed)
+        eig = of.min_eig_map(a)
+        assert abs(float(eig.max()) - float(g[f"s{seed}_eig_max"])) < 1e-6 * float(g[f"s{seed}_eig_max"])
+        assert np.array_equal(of.corners_from_eig(eig), g[f"s{seed}_p0"])
+        assert np.array_equal(of.corners_from_eig(eig, qualityLevel=0.01), g[f"s{seed}_dense"])
+        try:
+            import cv2  # noqa: F401
+        except ImportError:
+            continue
+        assert np.array_equal(of.good_features(a), g[f"s{seed}_p0"])
+        p1, st, err = of.pyr_lk(a, b, g[f"s{seed}_p0"])
+        assert np.array_equal(st, g[f"s{seed}_st"]) and np.allclose(p1, g[f"s{seed}_p1"], atol=1e-4)
