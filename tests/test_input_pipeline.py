@@ -1,5 +1,6 @@
 """Input pipeline: the audio memmap format / slicing host logic (CPU, bit-exact against the reference
 arithmetic and, in the authoring container, the reference's own loader), and the device front end (GPU)."""
+import importlib.util
 import os
 import sys
 
@@ -39,14 +40,25 @@ def test_audio_memmap_format_and_slicing(tmp_path):
 @pytest.mark.skipif(not os.path.isdir("/root/reference"), reason="the reference only exists in the authoring container")
 def test_reference_loader_reads_our_memmap(tmp_path):
     import types
+    import importlib
+    stubbed = []
     for name in ("matplotlib", "matplotlib.pyplot", "cv2", "wandb", "torchsummary"):
-        sys.modules.setdefault(name, types.ModuleType(name))
-    sys.modules["matplotlib"].pyplot = sys.modules["matplotlib.pyplot"]
+        try:
+            importlib.import_module(name)
+        except ImportError:
+            sys.modules[name] = types.ModuleType(name)
+            stubbed.append(name)
+    if "matplotlib" in stubbed:
+        sys.modules["matplotlib"].pyplot = sys.modules["matplotlib.pyplot"]
     sys.path.insert(0, "/root/reference")
     try:
-        import utilities as ref_util
+        spec = importlib.util.spec_from_file_location("ref_utilities", "/root/reference/utilities.py")
+        ref_util = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(ref_util)
     finally:
         sys.path.remove("/root/reference")
+        for name in stubbed:
+            sys.modules.pop(name, None)
     clips, idx = _make_map(tmp_path)
     m, index_map = ref_util.load_audio_map(str(tmp_path))
     assert m is not None and m.shape == (126234,)
