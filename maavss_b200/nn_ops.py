@@ -20,6 +20,52 @@ SYNC_BN_GROUP = None
 BN_GROUPS = 1
 
 
+# Weight gradients off the critical path.  Inside a train step nothing reads a weight gradient before the gradient exchange /
+# optimizer, so with ASYNC_WGRAD set (train_step does, around its micro-steps) every weight-gradient product (conv wgrad, bias
+# channel sums, Linear / LSTM wgrad) is issued on a companion stream of the stream its layer runs on; the backward chain of a
+# branch is then bn_bwd -> dgrad only.  join_wgrad_streams() is the barrier in front of the all-reduce / Adam.  Off by
+# default: a plain `.backward()` followed by a read of `.grad` stays correct without a join.
+ASYNC_WGRAD = False
+_wgrad_streams = {}
+_wgrad_active = set()
+
+
+class _WgradScope:
+    def __init__(self, *tensors):
+        self.tensors, self.ctx = tensors, None
+
+    def __enter__(self):
+        if not ASYNC_WGRAD:
+            return self
+        cur = torch.cuda.current_stream()
+        key = (cur.device_index, cur.cuda_stream)
+        side = _wgrad_streams.get(key)
+        if side is None:
+            side = _wgrad_streams[key] = torch.cuda.Stream(device=cur.device)
+        side.wait_stream(cur)
+        for t in self.tensors:
+            if t is not None:
+                t.record_stream(side)
+        _wgrad_active.add(side)
+        self.ctx = torch.cuda.stream(side)
+        self.ctx.__enter__()
+        return self
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            self.ctx.__exit__(*exc)
+        return False
+
+
+def join_wgrad_streams(target=None, clear=True):
+    """Make `target` (default: the current stream) wait for every outstanding weight-gradient stream."""
+    tgt = target if target is not None else torch.cuda.current_stream()
+    for s in list(_wgrad_active):
+        tgt.wait_stream(s)
+    if clear:
+        _wgrad_active.clear()
+
+
 class ConvDesc(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int) for n in "N Cin D H W Cout KD KH KW SD SH SW PD PH PW OD OH OW".split()]
 
@@ -126,13 +172,14 @@ class ConvFn(torch.autograd.Function):
             if not _conv_tc(desc, 1, dy5, _as5(weight).contiguous(), dx5):
                 check(lib().maavss_conv_dgrad(ctypes.byref(desc), fptr(dy5), fptr(weight), _null(), fptr(dx5), stream_ptr()))
             dx = dx5 if ctx.nd == 5 else dx5.squeeze(2)
-        tgt, acc, gw = _grad_slot(weight, ctx.needs_input_grad[1])
-        if tgt is not None and not _conv_wgrad_tc(desc, x5, dy5, tgt, acc):
-            check(lib().maavss_conv_wgrad(ctypes.byref(desc), fptr(x5), fptr(dy5), fptr(tgt), acc, stream_ptr()))
-        if bias is not None:
-            tgt, acc, gb = _grad_slot(bias, ctx.needs_input_grad[2])
-            if tgt is not None:
-                channel_sum(dy5, tgt, acc)
+        with _WgradScope(dy5, x5):
+            tgt, acc, gw = _grad_slot(weight, ctx.needs_input_grad[1])
+            if tgt is not None and not _conv_wgrad_tc(desc, x5, dy5, tgt, acc):
+                check(lib().maavss_conv_wgrad(ctypes.byref(desc), fptr(x5), fptr(dy5), fptr(tgt), acc, stream_ptr()))
+            if bias is not None:
+                tgt, acc, gb = _grad_slot(bias, ctx.needs_input_grad[2])
+                if tgt is not None:
+                    channel_sum(dy5, tgt, acc)
         return dx, gw, gb, None, None
 
 
@@ -396,14 +443,15 @@ class LinearActFn(torch.autograd.Function):
             dx = dx2.reshape(shp)
         w_t, w_acc, gw = _grad_slot(weight, ctx.needs_input_grad[1])
         b_t, b_acc, gb = _grad_slot(bias, bias is not None and ctx.needs_input_grad[2])
-        if w_t is not None:
-            if b_t is not None and b_acc != w_acc:          # mixed: give the bias its own pass below
-                linear_wgrad_into(dz, x2, w_t, None, w_acc)
+        with _WgradScope(dz, x2):
+            if w_t is not None:
+                if b_t is not None and b_acc != w_acc:          # mixed: give the bias its own pass below
+                    linear_wgrad_into(dz, x2, w_t, None, w_acc)
+                    check(L.maavss_colsum(fptr(dz), M, N, fptr(b_t), b_acc, stream_ptr()))
+                else:
+                    linear_wgrad_into(dz, x2, w_t, b_t, w_acc)
+            elif b_t is not None:
                 check(L.maavss_colsum(fptr(dz), M, N, fptr(b_t), b_acc, stream_ptr()))
-            else:
-                linear_wgrad_into(dz, x2, w_t, b_t, w_acc)
-        elif b_t is not None:
-            check(L.maavss_colsum(fptr(dz), M, N, fptr(b_t), b_acc, stream_ptr()))
         return dx, gw, gb, None, None
 
 

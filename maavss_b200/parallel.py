@@ -146,6 +146,7 @@ class EarlyGradAllReduce:
             return
         self.started = True
         self.side.wait_stream(torch.cuda.current_stream())
+        nn_ops.join_wgrad_streams(target=self.side, clear=False)      # the tail's weight gradients may still be in flight
         with torch.cuda.stream(self.side):
             allreduce_sum_(self.opt.flat.grad[self.offset:])
 

@@ -16,8 +16,9 @@ from . import layers, nn_ops, parallel, phasegram_ops
 
 
 class _TrainStepBase:
-    def __init__(self, model, optimizer, graph=True, warmup=2):
+    def __init__(self, model, optimizer, graph=True, warmup=2, async_wgrad=True):
         self.model, self.opt = model, optimizer
+        self.async_wgrad = async_wgrad
         self.use_graph, self.warmup = graph, warmup
         self._graph, self._static_in, self._static_out = None, None, None
         self.launches_per_step = None
@@ -31,10 +32,14 @@ class _TrainStepBase:
 
     def _eager(self, *inputs):
         self._running = True          # the LSTM hook of another step object built on the same model stays quiet
+        prev_async = nn_ops.ASYNC_WGRAD
+        nn_ops.ASYNC_WGRAD = self.async_wgrad
         try:
             out = self.micro_steps(*inputs)
         finally:
             self._running = False
+            nn_ops.ASYNC_WGRAD = prev_async
+        nn_ops.join_wgrad_streams()   # weight gradients ran on companion streams: all of them before the exchange / Adam
         if self.early is not None:
             self.early.finish()
         else:
