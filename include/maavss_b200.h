@@ -201,7 +201,7 @@ int maavss_lstm_step_bwd(const float* dy, const float* gates, const float* cells
  * cells (2, B, T, H) are outputs the backward needs (caller-owned).  The input projections and all weight / input gradients
  * run on the 3xTF32 tensor-core GEMM when B*T >= 32, the T recurrent steps are one launch each.
  * bilstm_bwd: dgates (2, B, T, 4H) is scratch / output; dx (B, T, I) and the four dw_* (same shapes as the weights) may be
- * NULL; accumulate != 0 adds into the dw_* (gradient accumulation).  workspace: maavss_bilstm_workspace_bytes(.., backward). */
+ * NULL; accumulate != 0 adds into the dw_* (gradient accumulation).  Order on the stream: T steps, dx, then the dw_*.  workspace: maavss_bilstm_workspace_bytes(.., backward). */
 long long maavss_bilstm_workspace_bytes(int B, int T, int I, int H, int backward);
 int maavss_bilstm_fwd(const float* x, const float* w_ih_fwd, const float* w_hh_fwd, const float* w_ih_rev, const float* w_hh_rev,
                       float* gin, float* gates, float* cells, float* y, int B, int T, int I, int H, void* workspace,
@@ -210,6 +210,12 @@ int maavss_bilstm_bwd(const float* dy, const float* x, const float* w_ih_fwd, co
                       const float* w_hh_rev, const float* gates, const float* cells, const float* y, float* dgates, float* dx,
                       float* dw_ih_fwd, float* dw_hh_fwd, float* dw_ih_rev, float* dw_hh_rev, int accumulate, int B, int T, int I, int H,
                       void* workspace, long long workspace_bytes, void* stream);
+/* The weight-gradient half of bilstm_bwd on its own (after a bilstm_bwd call with the four dw_* NULL, dgates kept): lets the
+ * caller enqueue it on another stream, off the chain dy -> dx that the rest of the backward pass waits for.  Own workspace
+ * of maavss_bilstm_workspace_bytes(.., 1) bytes (must not be shared with a bilstm_bwd still in flight). */
+int maavss_bilstm_wgrad(const float* x, const float* y, const float* dgates, float* dw_ih_fwd, float* dw_hh_fwd, float* dw_ih_rev,
+                        float* dw_hh_rev, int accumulate, int B, int T, int I, int H, void* workspace, long long workspace_bytes,
+                        void* stream);
 
 /* nn.MSELoss (mean): loss[0] = mean((a - b)^2)   (train.py:154-156).  workspace: maavss_reduce_workspace_bytes(8). */
 int maavss_mse_fwd(const float* a, const float* b, long long n, float* loss, void* workspace, void* stream);
@@ -222,6 +228,14 @@ int maavss_mse_bwd(const float* a, const float* b, const float* gout, long long 
  * grad_scale multiplies g (1/world_size after a sum all-reduce). */
 int maavss_adam_step(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2, float eps,
                      float weight_decay, void* state, float grad_scale, void* stream);
+/* The same step in two halves, for a train step that updates part of the arena early (train_step.EarlyTail: the LSTM / fc
+ * weights while the encoders still back-propagate): adam_prepare advances the device step counter and bias corrections ONCE
+ * per optimizer step, adam_apply updates any 16-byte aligned sub-range with them.  zero_grad != 0 also clears g[0..n)
+ * (optimizer.zero_grad(), train.py:162, fused into the same pass); max_ctas > 0 caps the grid (an update that shares the
+ * GPU with latency-bound kernels). */
+int maavss_adam_prepare(void* state, float lr, float beta1, float beta2, void* stream);
+int maavss_adam_apply(float* p, float* g, float* m, float* v, long long n, float beta1, float beta2, float eps, float weight_decay,
+                      const void* state, float grad_scale, int zero_grad, int max_ctas, void* stream);
 /* x[0..n) = value */
 int maavss_fill(float* x, long long n, float value, void* stream);
 

@@ -65,8 +65,9 @@ __global__ void adam_prepare_kernel(AdamState* st, float lr, float beta1, float 
 // torch.optim.Adam (no amsgrad, coupled weight decay): 4 reads + 3 writes of 4 B per parameter.
 __global__ void __launch_bounds__(256) adam_kernel(float4* __restrict__ p, const float4* __restrict__ g, float4* __restrict__ m,
                                                    float4* __restrict__ v, long long n4, float beta1, float beta2, float eps,
-                                                   float wd, const AdamState* __restrict__ st, float gscale) {
+                                                   float wd, const AdamState* __restrict__ st, float gscale, int zero_grad) {
     const float step_size = st->step_size, inv_bc2_sqrt = st->inv_bc2_sqrt;
+    float4* gw = const_cast<float4*>(g);
     for (long long q = (long long)blockIdx.x * 256 + threadIdx.x; q < n4; q += (long long)gridDim.x * 256) {
         float4 pp = p[q], gg = g[q], mm = m[q], vv = v[q];
         float* P = &pp.x;
@@ -85,11 +86,12 @@ __global__ void __launch_bounds__(256) adam_kernel(float4* __restrict__ p, const
         p[q] = pp;
         m[q] = mm;
         v[q] = vv;
+        if (zero_grad) gw[q] = make_float4(0.f, 0.f, 0.f, 0.f);       // optimizer.zero_grad() fused into the same pass
     }
 }
 
 __global__ void adam_tail_kernel(float* p, const float* g, float* m, float* v, long long start, long long n, float beta1,
-                                 float beta2, float eps, float wd, const AdamState* __restrict__ st, float gscale) {
+                                 float beta2, float eps, float wd, const AdamState* __restrict__ st, float gscale, int zero_grad) {
     const float step_size = st->step_size, inv_bc2_sqrt = st->inv_bc2_sqrt;
     const long long q = start + threadIdx.x;
     if (q >= n) return;
@@ -100,6 +102,7 @@ __global__ void adam_tail_kernel(float* p, const float* g, float* m, float* v, l
     m[q] = mm;
     v[q] = vv;
     p[q] -= step_size * (mm / (sqrtf(vv) * inv_bc2_sqrt + eps));
+    if (zero_grad) const_cast<float*>(g)[q] = 0.f;
 }
 
 __global__ void fill_kernel(float* __restrict__ x, long long n, float value) {
@@ -134,26 +137,42 @@ extern "C" int maavss_mse_bwd(const float* a, const float* b, const float* gout,
     return MAAVSS_OK;
 }
 
+extern "C" int maavss_adam_prepare(void* state, float lr, float beta1, float beta2, void* stream) {
+    MAAVSS_CHECK_ARG(state, "adam_prepare: null state");
+    adam_prepare_kernel<<<1, 1, 0, (cudaStream_t)stream>>>((AdamState*)state, lr, beta1, beta2);
+    MAAVSS_LAUNCH_CHECK();
+    return MAAVSS_OK;
+}
+
+extern "C" int maavss_adam_apply(float* p, float* g, float* m, float* v, long long n, float beta1, float beta2, float eps,
+                                 float weight_decay, const void* state, float grad_scale, int zero_grad, int max_ctas, void* stream) {
+    if (n == 0) return MAAVSS_OK;
+    MAAVSS_CHECK_ARG(p && g && m && v && state, "adam_apply: bad argument");
+    MAAVSS_CHECK_ARG(((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) % 16 == 0, "adam_apply: arenas must be 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+    const AdamState* as = (const AdamState*)state;
+    const long long n4 = n / 4;
+    if (n4 > 0) {
+        int grid = stream_grid(n4, 2);
+        if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
+        adam_kernel<<<grid, 256, 0, st>>>((float4*)p, (const float4*)g, (float4*)m, (float4*)v, n4, beta1, beta2, eps, weight_decay, as,
+                                         grad_scale, zero_grad);
+        MAAVSS_LAUNCH_CHECK();
+    }
+    if (n4 * 4 < n) {
+        adam_tail_kernel<<<1, 32, 0, st>>>(p, g, m, v, n4 * 4, n, beta1, beta2, eps, weight_decay, as, grad_scale, zero_grad);
+        MAAVSS_LAUNCH_CHECK();
+    }
+    return MAAVSS_OK;
+}
+
 extern "C" int maavss_adam_step(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2,
                                 float eps, float weight_decay, void* state, float grad_scale, void* stream) {
     if (n == 0) return MAAVSS_OK;
     MAAVSS_CHECK_ARG(p && g && m && v && state, "adam_step: bad argument");
-    MAAVSS_CHECK_ARG(((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) % 16 == 0, "adam_step: arenas must be 16-byte aligned");
-    cudaStream_t st = (cudaStream_t)stream;
-    AdamState* as = (AdamState*)state;
-    adam_prepare_kernel<<<1, 1, 0, st>>>(as, lr, beta1, beta2);
-    MAAVSS_LAUNCH_CHECK();
-    const long long n4 = n / 4;
-    if (n4 > 0) {
-        adam_kernel<<<stream_grid(n4, 2), 256, 0, st>>>((float4*)p, (const float4*)g, (float4*)m, (float4*)v, n4, beta1, beta2, eps,
-                                                       weight_decay, as, grad_scale);
-        MAAVSS_LAUNCH_CHECK();
-    }
-    if (n4 * 4 < n) {
-        adam_tail_kernel<<<1, 32, 0, st>>>(p, g, m, v, n4 * 4, n, beta1, beta2, eps, weight_decay, as, grad_scale);
-        MAAVSS_LAUNCH_CHECK();
-    }
-    return MAAVSS_OK;
+    int rc = maavss_adam_prepare(state, lr, beta1, beta2, stream);
+    if (rc) return rc;
+    return maavss_adam_apply(p, const_cast<float*>(g), m, v, n, beta1, beta2, eps, weight_decay, state, grad_scale, 0, 0, stream);
 }
 
 extern "C" int maavss_fill(float* x, long long n, float value, void* stream) {

@@ -270,6 +270,43 @@ extern "C" int maavss_bilstm_fwd(const float* x, const float* w_ih_fwd, const fl
     return MAAVSS_OK;
 }
 
+extern "C" int maavss_bilstm_wgrad(const float* x, const float* y, const float* dgates, float* dw_ih_fwd, float* dw_hh_fwd, float* dw_ih_rev,
+                                   float* dw_hh_rev, int accumulate, int B, int T, int I, int H, void* workspace, long long workspace_bytes,
+                                   void* stream) {
+    if (B == 0 || T == 0) return MAAVSS_OK;
+    MAAVSS_CHECK_ARG(x && y && dgates, "bilstm_wgrad: null argument");
+    MAAVSS_CHECK_ARG(workspace_bytes >= maavss_bilstm_workspace_bytes(B, T, I, H, 1), "bilstm_wgrad: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int M = B * T;
+    uint8_t* base = (uint8_t*)(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
+    long long g = maavss_bilstm_workspace_bytes(B, T, I, H, 1) - 256 - (long long)(al256(sizeof(float) * 2 * (size_t)B * H) +
+                  al256(sizeof(float) * 2 * (size_t)M * H) + al256(sizeof(float) * (size_t)M * I));
+    void* gws = base;
+    float* hprev = (float*)(base + g + al256(sizeof(float) * 2 * (size_t)B * H));
+    {
+        const long long n4 = 2LL * M * (H / 4);
+        int blocks = (int)((n4 + 255) / 256);
+        if (blocks > 148 * 8) blocks = 148 * 8;
+        lstm_hprev_kernel<<<blocks, 256, 0, st>>>(y, hprev, B, T, H / 4);
+        MAAVSS_LAUNCH_CHECK();
+    }
+    float* dw_ih[2] = {dw_ih_fwd, dw_ih_rev};
+    float* dw_hh[2] = {dw_hh_fwd, dw_hh_rev};
+    for (int d = 0; d < 2; ++d) {
+        const float* dg = dgates + (size_t)d * M * 4 * H;
+        int rc;
+        if (dw_ih[d]) {
+            rc = proj_wgrad(dg, x, dw_ih[d], M, 4 * H, I, accumulate, gws, g, stream);
+            if (rc) return rc;
+        }
+        if (dw_hh[d]) {
+            rc = proj_wgrad(dg, hprev + (size_t)d * M * H, dw_hh[d], M, 4 * H, H, accumulate, gws, g, stream);
+            if (rc) return rc;
+        }
+    }
+    return MAAVSS_OK;
+}
+
 extern "C" int maavss_bilstm_bwd(const float* dy, const float* x, const float* w_ih_fwd, const float* w_hh_fwd, const float* w_ih_rev,
                                  const float* w_hh_rev, const float* gates, const float* cells, const float* y, float* dgates, float* dx,
                                  float* dw_ih_fwd, float* dw_hh_fwd, float* dw_ih_rev, float* dw_hh_rev, int accumulate, int B, int T,
@@ -291,39 +328,24 @@ extern "C" int maavss_bilstm_bwd(const float* dy, const float* x, const float* w
         rc = maavss_lstm_step_bwd(dy, gates, cells, w_hh_fwd, w_hh_rev, dgates, dcell, B, T, H, s, stream);
         if (rc) return rc;
     }
-    {
-        const long long n4 = 2LL * M * (H / 4);
-        int blocks = (int)((n4 + 255) / 256);
-        if (blocks > 148 * 8) blocks = 148 * 8;
-        lstm_hprev_kernel<<<blocks, 256, 0, st>>>(y, hprev, B, T, H / 4);
-        MAAVSS_LAUNCH_CHECK();
-    }
+    // the input gradient first: it is what the rest of the backward pass waits for
     const float* w_ih[2] = {w_ih_fwd, w_ih_rev};
-    float* dw_ih[2] = {dw_ih_fwd, dw_ih_rev};
-    float* dw_hh[2] = {dw_hh_fwd, dw_hh_rev};
-    for (int d = 0; d < 2; ++d) {
+    for (int d = 0; d < 2 && dx; ++d) {
         const float* dg = dgates + (size_t)d * M * 4 * H;
-        if (dw_ih[d]) {
-            rc = proj_wgrad(dg, x, dw_ih[d], M, 4 * H, I, accumulate, gws, g, stream);
-            if (rc) return rc;
+        // dx[M, I] (+)= dg[M, 4H] w_ih[4H, I]: the second direction accumulates into the first one's result
+        if (M >= 32 && maavss_gemm_tf32x3_supported(I, M, 4 * H, 1, I, 0, 4 * H, I, 1) && maavss_gemm_tf32x3_workspace_bytes(I, M, 4 * H) <= g) {
+            rc = maavss_gemm_tf32x3(w_ih[d], 1, I, dg, 0, 4 * H, I, M, 4 * H, dx, I, 1, nullptr, 0, MAAVSS_ACT_NONE, 0.f, d, gws, g, stream);
+        } else if (d == 0) {
+            rc = maavss_linear_dgrad(dg, w_ih[d], dx, M, 4 * H, I, stream);
+        } else {
+            float* part = (float*)((uint8_t*)hprev + al256(sizeof(float) * 2 * (size_t)M * H));
+            rc = maavss_linear_dgrad(dg, w_ih[d], part, M, 4 * H, I, stream);
+            if (!rc) rc = maavss_add_noise(dx, part, 1.0f, dx, (long long)M * I, stream);      // dx += part (unfused a + b * 1)
         }
-        if (dw_hh[d]) {
-            rc = proj_wgrad(dg, hprev + (size_t)d * M * H, dw_hh[d], M, 4 * H, H, accumulate, gws, g, stream);
-            if (rc) return rc;
-        }
-        if (dx) {
-            // dx[M, I] (+)= dg[M, 4H] w_ih[4H, I]: the second direction accumulates into the first one's result
-            if (M >= 32 && maavss_gemm_tf32x3_supported(I, M, 4 * H, 1, I, 0, 4 * H, I, 1) && maavss_gemm_tf32x3_workspace_bytes(I, M, 4 * H) <= g) {
-                rc = maavss_gemm_tf32x3(w_ih[d], 1, I, dg, 0, 4 * H, I, M, 4 * H, dx, I, 1, nullptr, 0, MAAVSS_ACT_NONE, 0.f, d, gws, g, stream);
-            } else if (d == 0) {
-                rc = maavss_linear_dgrad(dg, w_ih[d], dx, M, 4 * H, I, stream);
-            } else {
-                float* part = (float*)((uint8_t*)hprev + al256(sizeof(float) * 2 * (size_t)M * H));
-                rc = maavss_linear_dgrad(dg, w_ih[d], part, M, 4 * H, I, stream);
-                if (!rc) rc = maavss_add_noise(dx, part, 1.0f, dx, (long long)M * I, stream);      // dx += part (unfused a + b * 1)
-            }
-            if (rc) return rc;
-        }
+        if (rc) return rc;
     }
+    if (dw_ih_fwd || dw_hh_fwd || dw_ih_rev || dw_hh_rev)
+        return maavss_bilstm_wgrad(x, y, dgates, dw_ih_fwd, dw_hh_fwd, dw_ih_rev, dw_hh_rev, accumulate, B, T, I, H, workspace, workspace_bytes,
+                                   stream);
     return MAAVSS_OK;
 }

@@ -217,19 +217,26 @@ __global__ void __launch_bounds__(kBnThreads) bn_reduce_g_kernel(const float* __
                ((double)s2[0] + (double)s2[1]) + ((double)s2[2] + (double)s2[3]), partial + (((size_t)g * C + c) * S + blockIdx.x) * 2);
 }
 
-__device__ __forceinline__ void stats_from_partial(const double* __restrict__ partial, int S, double count, float eps,
-                                                   double& mean, double& var) {
-    double s1 = 0, s2 = 0;
-    for (int s = 0; s < S; ++s) {
-        s1 += partial[2 * s];
-        s2 += partial[2 * s + 1];
+// Sum of the S (sum, sum-of-squares) partial pairs of one (group, channel) by the calling warp: every lane returns the totals.
+__device__ __forceinline__ void warp_sum_partials(const double* __restrict__ pp, int S, double& s1, double& s2) {
+    double a = 0, b = 0;
+    for (int s = threadIdx.x & 31; s < S; s += 32) {
+        a += pp[2 * s];
+        b += pp[2 * s + 1];
     }
-    mean = s1 / count;
-    var = s2 / count - mean * mean;
-    if (var < 0) var = 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, o);
+        b += __shfl_xor_sync(0xffffffffu, b, o);
+    }
+    s1 = a;
+    s2 = b;
 }
 
-// grid (chunks, N*C)
+// grid (chunks, C, G): CTA (k, c, g) normalises chunk k of the flattened (sample-in-group, inner) domain of channel c in
+// group g -- the same walk as the reduce kernel, so the deep layers (inner = 32..512 floats per row) still run full CTAs.
+// Warp 0 re-derives the (group, channel) statistics from the partials; CTA (0, c, 0) also applies the G running-statistics
+// updates of its channel in window order.
 __global__ void __launch_bounds__(kBnThreads) bn_apply_fused_kernel(const float* __restrict__ x, const double* __restrict__ partial,
                                                                     int S, int Ng, int G, double count, const float* __restrict__ gamma,
                                                                     const float* __restrict__ beta, float* __restrict__ running_mean,
@@ -237,40 +244,59 @@ __global__ void __launch_bounds__(kBnThreads) bn_apply_fused_kernel(const float*
                                                                     float momentum, float eps, int C, long long inner, int act,
                                                                     float slope, float* __restrict__ stats, float* __restrict__ y) {
     __shared__ float sh[2];
-    const int nc = blockIdx.y, c = nc % C, n = nc / C, g = n / Ng;
-    if (threadIdx.x == 0) {
-        double mean, var;
-        stats_from_partial(partial + ((size_t)g * C + c) * S * 2, S, count, eps, mean, var);
-        sh[0] = (float)mean;
-        sh[1] = (float)(1.0 / sqrt(var + (double)eps));
-        if (blockIdx.x == 0 && n == g * Ng) {
-            stats[((size_t)g * C + c) * 2] = sh[0];
-            stats[((size_t)g * C + c) * 2 + 1] = sh[1];
+    const int c = blockIdx.y, g = blockIdx.z;
+    if (threadIdx.x < 32) {
+        double s1, s2;
+        warp_sum_partials(partial + ((size_t)g * C + c) * S * 2, S, s1, s2);
+        const double mean = s1 / count;
+        double var = s2 / count - mean * mean;
+        if (var < 0) var = 0;
+        if (threadIdx.x == 0) {
+            sh[0] = (float)mean;
+            sh[1] = (float)(1.0 / sqrt(var + (double)eps));
+            if (blockIdx.x == 0) {
+                stats[((size_t)g * C + c) * 2] = sh[0];
+                stats[((size_t)g * C + c) * 2 + 1] = sh[1];
+            }
         }
-        if (blockIdx.x == 0 && n == 0) {          // one CTA per channel: running statistics, window order
+        if (blockIdx.x == 0 && g == 0) {
             if (running_mean) {
                 double rm = running_mean[c], rv = running_var[c];
                 for (int q = 0; q < G; ++q) {
-                    double m2, v2;
-                    stats_from_partial(partial + ((size_t)q * C + c) * S * 2, S, count, eps, m2, v2);
+                    warp_sum_partials(partial + ((size_t)q * C + c) * S * 2, S, s1, s2);
+                    const double m2 = s1 / count;
+                    double v2 = s2 / count - m2 * m2;
+                    if (v2 < 0) v2 = 0;
                     const double unbiased = count > 1 ? v2 * count / (count - 1) : v2;
                     // fp32 rounding after every window, like G sequential reference updates
                     rm = (double)(float)((1.0 - momentum) * rm + momentum * m2);
                     rv = (double)(float)((1.0 - momentum) * rv + momentum * unbiased);
                 }
-                running_mean[c] = (float)rm;
-                running_var[c] = (float)rv;
+                if (threadIdx.x == 0) {
+                    running_mean[c] = (float)rm;
+                    running_var[c] = (float)rv;
+                }
             }
-            if (c == 0 && nbt) nbt[0] += G;
+            if (threadIdx.x == 0 && c == 0 && nbt) nbt[0] += G;
         }
     }
     __syncthreads();
     const float mean = sh[0], invstd = sh[1];
     const float ga = gamma ? gamma[c] : 1.f, be = beta ? beta[c] : 0.f;
-    const float* xp = x + (size_t)nc * inner;
-    float* yp = y + (size_t)nc * inner;
-    for (long long i = (long long)blockIdx.x * kBnThreads + threadIdx.x; i < inner; i += (long long)gridDim.x * kBnThreads)
-        yp[i] = act_apply(fmaf((xp[i] - mean) * invstd, ga, be), act, slope);
+    const size_t row0 = (size_t)g * Ng * C + c;
+    if (bn_vec_ok(inner, x, y, y)) {
+        bn_walk<4>(Ng, inner, row0, C, [&](size_t off) {
+            const float4 v = *reinterpret_cast<const float4*>(x + off);
+            float4 o;
+            o.x = act_apply(fmaf((v.x - mean) * invstd, ga, be), act, slope);
+            o.y = act_apply(fmaf((v.y - mean) * invstd, ga, be), act, slope);
+            o.z = act_apply(fmaf((v.z - mean) * invstd, ga, be), act, slope);
+            o.w = act_apply(fmaf((v.w - mean) * invstd, ga, be), act, slope);
+            *reinterpret_cast<float4*>(y + off) = o;
+        });
+    } else {
+        bn_walk<1>(Ng, inner, row0, C, [&](size_t off) { y[off] = act_apply(fmaf((x[off] - mean) * invstd, ga, be), act, slope); });
+    }
 }
 
 __global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_g_kernel(const float* __restrict__ dy, const float* __restrict__ y,
@@ -304,6 +330,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_g_kernel(const float
                ((double)s2[0] + (double)s2[1]) + ((double)s2[2] + (double)s2[3]), partial + (((size_t)g * C + c) * S + blockIdx.x) * 2);
 }
 
+// grid (chunks, C, G), walk as bn_apply_fused_kernel.  CTA (0, c, 0) also emits dgamma / dbeta of its channel.
 __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_fused_kernel(const float* __restrict__ dy, const float* __restrict__ y,
                                                                         const float* __restrict__ x, const float* __restrict__ stats,
                                                                         const float* __restrict__ gamma, const double* __restrict__ partial,
@@ -312,30 +339,25 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_fused_kernel(const fl
                                                                         float slope, float* __restrict__ dgamma,
                                                                         float* __restrict__ dbeta, int accumulate, float* __restrict__ dx) {
     __shared__ float sh[2];
-    const int nc = blockIdx.y, c = nc % C, n = nc / C, g = n / Ng;
-    if (threadIdx.x == 0) {
-        double s1 = 0, s2 = 0;
-        const double* pp = partial + ((size_t)g * C + c) * S * 2;
-        for (int s = 0; s < S; ++s) {
-            s1 += pp[2 * s];
-            s2 += pp[2 * s + 1];
+    const int c = blockIdx.y, g = blockIdx.z;
+    if (threadIdx.x < 32) {
+        double s1, s2;
+        warp_sum_partials(partial + ((size_t)g * C + c) * S * 2, S, s1, s2);
+        if (threadIdx.x == 0) {
+            sh[0] = (float)(s1 / count);
+            sh[1] = (float)(s2 / count);
         }
-        sh[0] = (float)(s1 / count);
-        sh[1] = (float)(s2 / count);
-        if (blockIdx.x == 0 && n == 0 && (dgamma || dbeta)) {
+        if (blockIdx.x == 0 && g == 0 && (dgamma || dbeta)) {
             double t1 = 0, t2 = 0;
             for (int q = 0; q < G; ++q) {            // window order, fp32 accumulation like G sequential backward passes
-                double a1 = 0, a2 = 0;
-                const double* pq = partial_local + ((size_t)q * C + c) * S * 2;
-                for (int s = 0; s < S; ++s) {
-                    a1 += pq[2 * s];
-                    a2 += pq[2 * s + 1];
-                }
-                t1 = (double)(float)(t1 + (float)a1);
-                t2 = (double)(float)(t2 + (float)a2);
+                warp_sum_partials(partial_local + ((size_t)q * C + c) * S * 2, S, s1, s2);
+                t1 = (double)(float)(t1 + (float)s1);
+                t2 = (double)(float)(t2 + (float)s2);
             }
-            if (dgamma) dgamma[c] = accumulate ? dgamma[c] + (float)t2 : (float)t2;
-            if (dbeta) dbeta[c] = accumulate ? dbeta[c] + (float)t1 : (float)t1;
+            if (threadIdx.x == 0) {
+                if (dgamma) dgamma[c] = accumulate ? dgamma[c] + (float)t2 : (float)t2;
+                if (dbeta) dbeta[c] = accumulate ? dbeta[c] + (float)t1 : (float)t1;
+            }
         }
     }
     __syncthreads();
@@ -343,11 +365,27 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_fused_kernel(const fl
     const float mean = stats[((size_t)g * C + c) * 2], invstd = stats[((size_t)g * C + c) * 2 + 1];
     const float scale = (gamma ? gamma[c] : 1.f) * invstd;
     const float c0 = sh[0], c1 = sh[1];
-    const size_t base = (size_t)nc * inner;
-    for (long long i = (long long)blockIdx.x * kBnThreads + threadIdx.x; i < inner; i += (long long)gridDim.x * kBnThreads) {
-        const float dz = dy[base + i] * act_grad(y[base + i], act, slope);
-        const float xh = (x[base + i] - mean) * invstd;
-        dx[base + i] = scale * (dz - c0 - xh * c1);
+    const size_t row0 = (size_t)g * Ng * C + c;
+    if (bn_vec_ok(inner, dy, y, x) && bn_vec_ok(inner, dx, dx, dx)) {
+        bn_walk<4>(Ng, inner, row0, C, [&](size_t off) {
+            const float4 d4 = *reinterpret_cast<const float4*>(dy + off), y4 = *reinterpret_cast<const float4*>(y + off),
+                         x4 = *reinterpret_cast<const float4*>(x + off);
+            const float dv[4] = {d4.x, d4.y, d4.z, d4.w}, yv[4] = {y4.x, y4.y, y4.z, y4.w}, xv[4] = {x4.x, x4.y, x4.z, x4.w};
+            float o[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float dz = dv[k] * act_grad(yv[k], act, slope);
+                const float xh = (xv[k] - mean) * invstd;
+                o[k] = scale * (dz - c0 - xh * c1);
+            }
+            *reinterpret_cast<float4*>(dx + off) = make_float4(o[0], o[1], o[2], o[3]);
+        });
+    } else {
+        bn_walk<1>(Ng, inner, row0, C, [&](size_t off) {
+            const float dz = dy[off] * act_grad(y[off], act, slope);
+            const float xh = (x[off] - mean) * invstd;
+            dx[off] = scale * (dz - c0 - xh * c1);
+        });
     }
 }
 
@@ -364,6 +402,13 @@ __global__ void act_bwd_kernel(const float* __restrict__ dy, const float* __rest
 inline int ew_grid(long long n) {
     long long b = (n + 1023) / 1024;
     if (b > 148 * 8) b = 148 * 8;
+    return (int)(b < 1 ? 1 : b);
+}
+// chunks of one (group, channel) for the grouped apply kernels: >= 2048 elements per CTA, at most ~8 CTAs per SM over the grid
+inline int group_chunks(long long per_gc, long long gc) {
+    long long b = (per_gc + 2047) / 2048;
+    const long long cap = (148LL * 8 + gc - 1) / gc;
+    if (b > cap) b = cap;
     return (int)(b < 1 ? 1 : b);
 }
 inline int inner_chunks(long long inner, long long rows) {
@@ -460,9 +505,9 @@ extern "C" int maavss_bn_apply_grouped(const float* x, const double* partial, in
                                        float* y, void* stream) {
     if ((long long)N * C * inner == 0) return MAAVSS_OK;
     MAAVSS_CHECK_ARG(x && partial && stats && y && C > 0, "bn_apply_grouped: bad argument");
-    MAAVSS_CHECK_ARG(groups >= 1 && N % groups == 0 && (long long)N * C <= 65535 && count > 0, "bn_apply_grouped: bad batch / groups");
+    MAAVSS_CHECK_ARG(groups >= 1 && groups <= 65535 && C <= 65535 && N % groups == 0 && count > 0, "bn_apply_grouped: bad batch / groups");
     const int Ng = N / groups, S = maavss_bn_splits(Ng, C, inner);
-    dim3 grid(inner_chunks(inner, (long long)N * C), N * C);
+    dim3 grid(group_chunks((long long)Ng * inner, (long long)C * groups), C, groups);
     bn_apply_fused_kernel<<<grid, kBnThreads, 0, (cudaStream_t)stream>>>(x, partial, S, Ng, groups, count, gamma, beta, running_mean,
                                                                         running_var, num_batches_tracked, momentum, eps, C, inner,
                                                                         act, slope, stats, y);
@@ -487,9 +532,9 @@ extern "C" int maavss_bn_bwd_apply_grouped(const float* dy, const float* y, cons
                                            float* dx, void* stream) {
     if ((long long)N * C * inner == 0) return MAAVSS_OK;
     MAAVSS_CHECK_ARG(dy && y && x && stats && partial && partial_local && C > 0, "bn_bwd_apply_grouped: bad argument");
-    MAAVSS_CHECK_ARG(groups >= 1 && N % groups == 0 && (long long)N * C <= 65535 && count > 0, "bn_bwd_apply_grouped: bad batch / groups");
+    MAAVSS_CHECK_ARG(groups >= 1 && groups <= 65535 && C <= 65535 && N % groups == 0 && count > 0, "bn_bwd_apply_grouped: bad batch / groups");
     const int Ng = N / groups, S = maavss_bn_splits(Ng, C, inner);
-    dim3 grid(inner_chunks(inner, (long long)N * C), N * C);
+    dim3 grid(group_chunks((long long)Ng * inner, (long long)C * groups), C, groups);
     bn_bwd_apply_fused_kernel<<<grid, kBnThreads, 0, (cudaStream_t)stream>>>(dy, y, x, stats, gamma, partial, partial_local, S, Ng, groups,
                                                                             count, C, inner, act, slope, dgamma, dbeta, accumulate, dx);
     MAAVSS_LAUNCH_CHECK();

@@ -411,8 +411,15 @@ __global__ void __launch_bounds__(256) finalize_kernel(const float* __restrict__
     const long long n = rows * cols;
     for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
         const long long r = i / cols, c = i - r * cols;
-        float v = 0.f;
-        for (int s = 0; s < splits; ++s) v += ws[(size_t)s * n + i];
+        // 8 partials in flight per thread (the sum is latency-bound otherwise: up to 37 dependent L2 loads); fixed order
+        float v8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        int s = 0;
+        for (; s + 8 <= splits; s += 8) {
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v8[u] += __ldcs(ws + (size_t)(s + u) * n + i);
+        }
+        for (int u = 0; s < splits; ++s, ++u) v8[u] += __ldcs(ws + (size_t)s * n + i);
+        float v = ((v8[0] + v8[1]) + (v8[2] + v8[3])) + ((v8[4] + v8[5]) + (v8[6] + v8[7]));
         if (bias) v += __ldg(bias + (bias_on_cols ? c : r));
         v = apply_act(v, act, slope);
         float* o = out + r * ldc + c;
@@ -523,7 +530,7 @@ extern "C" int maavss_gemm_tf32x3(const float* A, int a_mn_major, long long lda,
         const long long rows = out_transposed ? Q : P, cols = out_transposed ? P : Q;
         // bias index in terms of the stored (rows, cols): per p -> rows unless transposed
         const int bias_on_cols = out_transposed ? !bias_on_q : bias_on_q;
-        int blocks = (int)((rows * cols + 1023) / 1024);
+        int blocks = (int)((rows * cols + 255) / 256);       // one element per thread while the grid fits: the sum is a latency chain
         if (blocks > 148 * 8) blocks = 148 * 8;
         tg3::finalize_kernel<<<blocks, 256, 0, st>>>(p.ws, p.splits, rows, cols, out, ldc, bias, bias_on_cols, act, slope, accumulate);
         MAAVSS_LAUNCH_CHECK();

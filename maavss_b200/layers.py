@@ -163,6 +163,17 @@ def _side_stream(device):
     return s
 
 
+_report_streams = {}
+
+
+def _report_stream(device):
+    """Stream of the loss values a train step only reports (train_step.FusionTrainStep): off the forward -> backward chain."""
+    s = _report_streams.get(device)
+    if s is None:
+        s = _report_streams[device] = torch.cuda.Stream(device=device)
+    return s
+
+
 def run_pair(seq_main, x_main, seq_side, x_side):
     """(seq_main(x_main), seq_side(x_side)) with the two FusedSequentials interleaved on the current and a side stream."""
     if not (PARALLEL_BRANCHES and x_main.is_cuda and x_side.is_cuda):

@@ -496,9 +496,15 @@ class LSTMFn(torch.autograd.Function):
         dx = torch.empty(B, T, I, device=dev, dtype=torch.float32) if ctx.needs_input_grad[0] else None
         nbytes = L.maavss_bilstm_workspace_bytes(B, T, I, H, 1)
         ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+        # recurrent steps + input gradient on this stream; the four weight gradients on the companion stream
         check(L.maavss_bilstm_bwd(fptr(dy), fptr(x), fptr(w_ih_f), fptr(w_hh_f), fptr(w_ih_r), fptr(w_hh_r), fptr(gates), fptr(cells),
-                                  fptr(y), fptr(dgates), _opt(dx), *[_opt(t) for t, _, _ in slots], acc, B, T, I, H, dptr(ws),
+                                  fptr(y), fptr(dgates), _opt(dx), _null(), _null(), _null(), _null(), acc, B, T, I, H, dptr(ws),
                                   ctypes.c_longlong(nbytes), stream_ptr()))
+        if any(t is not None for t, _, _ in slots):
+            with _WgradScope(dgates, x, y):
+                ws2 = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+                check(L.maavss_bilstm_wgrad(fptr(x), fptr(y), fptr(dgates), *[_opt(t) for t, _, _ in slots], acc, B, T, I, H, dptr(ws2),
+                                            ctypes.c_longlong(nbytes), stream_ptr()))
         grads = [dx]
         for (t, a, ret), w in zip(slots, (w_ih_f, w_hh_f, w_ih_r, w_hh_r)):
             grads.append(t if isinstance(ret, str) or ret is not None else None)
@@ -536,6 +542,29 @@ class MSEFn(torch.autograd.Function):
 
 def mse_loss(a, b):
     return MSEFn.apply(a, b)
+
+
+_consts = {}
+
+
+def const_scalar(value, device):
+    """A cached fp32 device scalar (gradient seeds of the train steps: no fill kernel per step)."""
+    key = (float(value), device.type, device.index)
+    t = _consts.get(key)
+    if t is None:
+        t = _consts[key] = torch.full((), float(value), device=device, dtype=torch.float32)
+    return t
+
+
+def mse_grad(a, b, seed):
+    """d(seed * mean((a - b)^2)) / da without the forward reduction: what MSEFn.backward returns for `gout = seed` (a device
+    scalar).  The train steps seed the backward pass with it, so the loss VALUE (reporting only) leaves the critical path."""
+    a, b = a.detach().contiguous(), b.detach().contiguous()
+    if a.shape != b.shape:
+        raise RuntimeError(f"mse_grad: shapes differ {tuple(a.shape)} vs {tuple(b.shape)}")
+    da = torch.empty_like(a)
+    check(lib().maavss_mse_bwd(fptr(a), fptr(b), fptr(seed), a.numel(), fptr(da), 0, stream_ptr()))
+    return da
 
 
 def stack_windows(x, windows, hop, span):

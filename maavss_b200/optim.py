@@ -81,14 +81,38 @@ class Adam(torch.optim.Optimizer):
         self.flat.zero_grad()
 
     @torch.no_grad()
-    def step(self, closure=None):
-        loss = closure() if closure is not None else None
+    def prepare(self):
+        """First half of a step: advance the device step counter / bias corrections (once per optimizer step)."""
         g = self.param_groups[0]
         self.step_count += 1
-        check(lib().maavss_adam_step(fptr(self.flat.data), fptr(self.flat.grad), fptr(self.exp_avg), fptr(self.exp_avg_sq),
-                                     self.flat.numel, g["lr"], g["betas"][0], g["betas"][1], g["eps"], g["weight_decay"],
-                                     dptr(self.dev_state), self.grad_scale, stream_ptr()))
+        check(lib().maavss_adam_prepare(dptr(self.dev_state), g["lr"], g["betas"][0], g["betas"][1], stream_ptr()))
+
+    @torch.no_grad()
+    def apply_range(self, lo=0, hi=None, zero_grad=False, max_ctas=0):
+        """Second half: update arena elements [lo, hi) (multiples of 4) with the prepared step; optionally clear their gradients."""
+        hi = self.flat.numel if hi is None else hi
+        if hi <= lo:
+            return
+        if lo % _ALIGN:
+            raise ValueError("apply_range: lo must be a multiple of 4 elements")
+        g = self.param_groups[0]
+        f = self.flat
+        check(lib().maavss_adam_apply(fptr(f.data[lo:hi]), fptr(f.grad[lo:hi]), fptr(self.exp_avg[lo:hi]), fptr(self.exp_avg_sq[lo:hi]),
+                                      hi - lo, g["betas"][0], g["betas"][1], g["eps"], g["weight_decay"], dptr(self.dev_state),
+                                      self.grad_scale, int(zero_grad), max_ctas, stream_ptr()))
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = closure() if closure is not None else None
+        self.prepare()
+        self.apply_range()
         return loss
+
+    @torch.no_grad()
+    def step_and_zero_grad(self):
+        """optimizer.step(); optimizer.zero_grad() (train.py:161-162) as one pass over the arenas."""
+        self.prepare()
+        self.apply_range(zero_grad=True)
 
     def _sync_step_state(self):
         """The device counter is the truth (a captured train step advances it on every replay without passing through

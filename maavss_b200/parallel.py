@@ -127,41 +127,58 @@ def allreduce_gradients(optimizer):
     optimizer.grad_scale = 1.0 / _WORLD
 
 
+# CTAs of the early Adam pass: it streams ~1 GB next to the latency-bound encoder backward and must not take its SM slots
+EARLY_ADAM_CTAS = int(os.environ.get("MAAVSS_EARLY_ADAM_CTAS", "148"))
+EARLY_ADAM = os.environ.get("MAAVSS_EARLY_ADAM", "1") != "0"
+
+
 class EarlyGradAllReduce:
-    """Overlap most of the gradient exchange with the rest of the backward pass.
+    """Take the tail of the optimizer step off the critical path.
 
-    The flat gradient arena is split at `offset`: everything from `offset` on (the LSTM / fc / head weights of the
-    fusion models, 98 % of the parameters, whose gradients are final once the LSTM backward has run) is all-reduced on a
-    side stream as soon as `start()` is called from an autograd hook, while the convolutional encoders are still
-    back-propagating on the main stream; `finish()` reduces the head of the arena and joins the side stream.  Both
-    streams' work is captured when the step is recorded into a CUDA graph."""
+    The flat arenas are split at `offset`: everything from `offset` on (the LSTM / fc / head weights of the fusion models,
+    98 % of the parameters, whose gradients are final once the LSTM backward has run) is handled on a side stream as soon
+    as `start()` is called from an autograd hook, while the convolutional encoders are still back-propagating on the main
+    stream: the data-parallel all-reduce of that part of the gradient arena (N > 1), then -- `early_adam` -- its Adam
+    update and zero_grad.  No kernel of the remaining backward pass reads those parameters (the encoders sit in front of
+    the LSTM).  `finish()` is the rest of the optimizer step: exchange + Adam + zero_grad of the head, joined with the
+    side stream.  Both streams' work is captured when the step is recorded into a CUDA graph."""
 
-    def __init__(self, optimizer, offset):
-        self.opt, self.offset = optimizer, int(offset)
-        self.side = torch.cuda.Stream() if _GROUP is not None else None
+    def __init__(self, optimizer, offset, early_adam=True):
+        self.opt, self.offset, self.early_adam = optimizer, int(offset), early_adam and EARLY_ADAM
+        self.side = torch.cuda.Stream()
         self.started = False
+        if _GROUP is not None:
+            optimizer.grad_scale = 1.0 / _WORLD
 
     def start(self):
-        if _GROUP is None or self.started:
+        if self.started:
             return
         self.started = True
         self.side.wait_stream(torch.cuda.current_stream())
         nn_ops.join_wgrad_streams(target=self.side, clear=False)      # the tail's weight gradients may still be in flight
         with torch.cuda.stream(self.side):
-            allreduce_sum_(self.opt.flat.grad[self.offset:])
+            if _GROUP is not None:
+                allreduce_sum_(self.opt.flat.grad[self.offset:])
+            if self.early_adam:
+                self.opt.prepare()
+                self.opt.apply_range(self.offset, None, zero_grad=True, max_ctas=EARLY_ADAM_CTAS)
 
     def finish(self):
-        if _GROUP is None:
-            return
-        g = self.opt.flat.grad
+        """Everything of optimizer.step(); optimizer.zero_grad() (and the gradient exchange) that start() has not done."""
+        opt, g = self.opt, self.opt.flat.grad
         if self.started:
-            if self.offset > 0:
+            if _GROUP is not None and self.offset > 0:
                 allreduce_sum_(g[:self.offset])
             torch.cuda.current_stream().wait_stream(self.side)
+            if self.early_adam:
+                opt.apply_range(0, self.offset, zero_grad=True)
+            else:
+                opt.step_and_zero_grad()
         else:
-            allreduce_sum_(g)
+            if _GROUP is not None:
+                allreduce_sum_(g)
+            opt.step_and_zero_grad()
         self.started = False
-        self.opt.grad_scale = 1.0 / _WORLD
 
 
 def allreduce_max_(t):

@@ -10,9 +10,14 @@ B200 execution model: the whole step (4 forward/backward micro-steps, the data-p
 Adam kernel) is captured ONCE into a CUDA graph over static input buffers and replayed per step -- no tracing compiler,
 no per-op Python on the replay path.  `graph=False` runs the same code eagerly (what an unchanged train.py does).
 """
+import os
+
 import torch
 
 from . import layers, nn_ops, parallel, phasegram_ops
+
+
+REPORT_STREAM = os.environ.get("MAAVSS_REPORT_STREAM", "1") != "0"      # benchmarks only: 0 keeps the reported losses on the main stream
 
 
 class _TrainStepBase:
@@ -41,11 +46,10 @@ class _TrainStepBase:
             nn_ops.ASYNC_WGRAD = prev_async
         nn_ops.join_wgrad_streams()   # weight gradients ran on companion streams: all of them before the exchange / Adam
         if self.early is not None:
-            self.early.finish()
+            self.early.finish()           # exchange + Adam + zero_grad of whatever the early hook has not done yet
         else:
             parallel.allreduce_gradients(self.opt)
-        self.opt.step()
-        self.opt.zero_grad()
+            self.opt.step_and_zero_grad()
         return out
 
     def _capture(self, inputs):
@@ -110,10 +114,11 @@ class FusionTrainStep(_TrainStepBase):
 
     def _setup_early_allreduce(self, enabled):
         """avse_model.AV_Fusion_Model.forward trains [encoders | lstm fc1 fc2 (decoders: unused) a_fc1 v_fc1]: from the
-        first LSTM weight to the end of the arena nothing receives gradient after the LSTM backward, so that tail is
-        exchanged while the encoders back-propagate (the hook fires when the LSTM's input gradient exists)."""
+        first LSTM weight to the end of the arena nothing receives gradient -- and no parameter is read -- after the LSTM
+        backward, so that tail is exchanged (N > 1) and Adam-updated while the encoders back-propagate (the hook fires
+        when the LSTM's input gradient exists)."""
         m = self.model
-        if not enabled or parallel.world_size() == 1 or getattr(m, "VARIANT", None) != "fc" or not self.batch_windows:
+        if not enabled or getattr(m, "VARIANT", None) != "fc" or not self.batch_windows:
             return
         first = next(m.lstm.parameters())
         flat = self.opt.flat
@@ -155,15 +160,25 @@ class FusionTrainStep(_TrainStepBase):
         nn_ops.BN_GROUPS = G
         try:
             yh_a, yh_v, _ = self.model(xa, pgram)
+            # What the sequential loop reports -- the last window's losses -- is a side-stream job: the backward pass is
+            # seeded with d loss / d yh directly (same kernel and seeds as MSELoss.backward under loss.backward()), so no
+            # loss reduction sits between the forward and the backward pass.
+            cur = torch.cuda.current_stream(xa.device)
+            rep = layers._report_stream(xa.device) if REPORT_STREAM else cur
+            rep.wait_stream(cur)
+            with torch.cuda.stream(rep), torch.no_grad():
+                a_loss = nn_ops.mse_loss(yh_a[-B:], ya[-B:])
+                v_loss = nn_ops.mse_loss(yh_v[-B:], pgram[-B:])
+                last = (a_loss + self.loss_coeff * v_loss) / G
             # equal window sizes: the MSE over the stack is the mean of the per-window MSEs = sum_j (.)_j / num_seq
-            loss = nn_ops.mse_loss(yh_a, ya) + self.loss_coeff * nn_ops.mse_loss(yh_v, pgram)
-            loss.backward()
+            ga = nn_ops.mse_grad(yh_a, ya, nn_ops.const_scalar(1.0, xa.device))
+            gv = nn_ops.mse_grad(yh_v, pgram, nn_ops.const_scalar(self.loss_coeff, xa.device))
+            torch.autograd.backward([yh_a, yh_v], [ga, gv])
+            cur.wait_stream(rep)
+            for t in (last, a_loss, v_loss):
+                t.record_stream(cur)
         finally:
             nn_ops.BN_GROUPS = 1
-        with torch.no_grad():                     # what the sequential loop reports: the last window's losses
-            a_loss = nn_ops.mse_loss(yh_a[-B:], ya[-B:])
-            v_loss = nn_ops.mse_loss(yh_v[-B:], pgram[-B:])
-            last = (a_loss + self.loss_coeff * v_loss) / G
         return last, a_loss, v_loss
 
     def micro_steps(self, x_stft, y_stft, attn):
