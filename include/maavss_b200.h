@@ -112,6 +112,15 @@ int maavss_conv_wgrad_tc(const maavss_conv_desc* d, const float* x, const float*
 /* out[c] (+)= sum_{n,i} x[n, c, i]   (bias gradients). workspace: maavss_reduce_workspace_bytes(C). */
 int maavss_channel_sum(const float* x, int N, int C, long long inner, float* out, int accumulate, void* workspace, void* stream);
 int maavss_reduce_workspace_bytes(int C);
+/* Allocation-free variant of maavss_channel_sum.  NO counterpart in the reference: added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  Same kernels and results as maavss_channel_sum, but the partial sums live in a static 512 KB device array inside
+ * the library (held by every GPU that loads it until exit) instead of a caller workspace; the call allocates nothing.
+ * Limit: C <= maavss_channel_sum_static_max_channels() = 4096, larger C is rejected with MAAVSS_ERR_INVALID.  All calls share
+ * the array: calls that may overlap on the GPU (different streams without ordering) race -- serialise them.  The first call
+ * on a device resolves the array's address (cudaGetSymbolAddress): make it outside stream capture. */
+int maavss_channel_sum_static(const float* x, int N, int C, long long inner, float* out, int accumulate, void* stream);
+int maavss_channel_sum_static_max_channels(void);
 
 /* Activations: 0 = identity, 1 = tanh, 2 = leaky_relu(slope), 3 = sigmoid. */
 #define MAAVSS_ACT_NONE 0

@@ -69,3 +69,61 @@ extern "C" int maavss_channel_sum(const float* x, int N, int C, long long inner,
     MAAVSS_LAUNCH_CHECK();
     return MAAVSS_OK;
 }
+
+// ------------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of maavss_channel_sum (no counterpart in the reference):
+// the [C][16] double partial sums live in a file-scope device array instead of a caller workspace, so the call
+// needs no cudaMalloc'd scratch -- for callers under CUDA graph capture, tight serving loops or harnesses that forbid
+// allocation.  512 KB of device memory per GPU that loads the library, held until exit.  Every call shares the array:
+// stage 1 overwrites all 16 * C entries that stage 2 reads (nothing has to start at zero), but two calls that overlap on
+// the GPU (different streams, no ordering) race on it.
+#include <mutex>
+
+constexpr int kStaticSumMaxC = 4096;
+static __device__ __align__(256) double g_channel_sum_scratch[(size_t)kSumSplits * kStaticSumMaxC];
+
+namespace {
+
+// Device address of g_channel_sum_scratch on the current device.  In host code the array's name is only a handle for the
+// runtime, not a device pointer: the address comes from cudaGetSymbolAddress, looked up once per device with that device
+// current (no allocation; it may load the module, so the first call per device belongs outside stream capture).
+int static_scratch_ptr(double** out) {
+    constexpr int kMaxDev = 64;
+    static double* ptrs[kMaxDev] = {};
+    static std::mutex mu;
+    int dev = -1;
+    MAAVSS_CUDA(cudaGetDevice(&dev));
+    MAAVSS_CHECK_ARG(dev >= 0 && dev < kMaxDev, "channel_sum_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        double* p = nullptr;
+        MAAVSS_CUDA(cudaGetSymbolAddress((void**)&p, g_channel_sum_scratch));
+        MAAVSS_CHECK_ARG(p != nullptr, "channel_sum_static: cudaGetSymbolAddress returned a null address");
+        ptrs[dev] = p;
+    }
+    *out = ptrs[dev];
+    return MAAVSS_OK;
+}
+
+}  // namespace
+
+extern "C" int maavss_channel_sum_static_max_channels(void) { return kStaticSumMaxC; }
+
+extern "C" int maavss_channel_sum_static(const float* x, int N, int C, long long inner, float* out, int accumulate, void* stream) {
+    if (C == 0) return MAAVSS_OK;
+    MAAVSS_CHECK_ARG(x && out, "channel_sum_static: null argument");
+    MAAVSS_CHECK_ARG(N >= 0 && C > 0 && inner >= 0, "channel_sum_static: bad shape N=%d C=%d inner=%lld", N, C, inner);
+    MAAVSS_CHECK_ARG(C <= kStaticSumMaxC,
+                     "channel_sum_static: C=%d exceeds the static scratch limit of %d channels (use maavss_channel_sum with a workspace)", C,
+                     kStaticSumMaxC);
+    double* ws = nullptr;
+    int rc = static_scratch_ptr(&ws);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    dim3 grid(kSumSplits, C);
+    channel_sum_partial<<<grid, 256, 0, st>>>(x, N, C, inner, ws);
+    MAAVSS_LAUNCH_CHECK();
+    channel_sum_final<<<ceil_div(C, 128), 128, 0, st>>>(ws, C, out, accumulate);
+    MAAVSS_LAUNCH_CHECK();
+    return MAAVSS_OK;
+}
