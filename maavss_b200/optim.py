@@ -60,7 +60,7 @@ class Adam(torch.optim.Optimizer):
     """torch.optim.Adam(params, lr, betas, eps, weight_decay) semantics, one kernel per step over the flat arena.
 
     Parameters whose ``requires_grad`` is False at step time keep their value (their arena gradient is zero and so
-    are their moments unless they were trained before; see DESIGN.md "frozen parameters")."""
+    are their moments unless they were trained before: Adam's update of a zero gradient with zero moments is zero)."""
 
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, grad_scale=1.0):
         params = list(params)
