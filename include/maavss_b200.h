@@ -109,6 +109,28 @@ int maavss_conv_wgrad_tc_supported(const maavss_conv_desc* d);
 long long maavss_conv_wgrad_tc_workspace_bytes(const maavss_conv_desc* d);
 int maavss_conv_wgrad_tc(const maavss_conv_desc* d, const float* x, const float* dy, float* dw, int accumulate, void* workspace,
                          long long workspace_bytes, void* stream);
+/* fp32-accurate tensor-core path (3xTF32 on tcgen05, tc_gemm3.cu) for the mid / deep Conv2d layers of the fusion encoders
+ * (avse_model.py:427-446,474-502; avse_model_conv.py:427-500): same products as maavss_conv_fwd / _dgrad / _wgrad, <= 5e-6 of
+ * torch fp32.  supported(): 2-D layers (D = KD = 1) with Cin >= 8, Cout >= 16 and a multiple of 4, Cin*KH*KW a multiple of 4,
+ * OH*OW a multiple of 32, N*OH*OW >= 128 and an im2col matrix of <= 512 MB.
+ *   fwd    writes the im2col matrix col (N*OH*OW, Cin*KH*KW) (caller-owned, maavss_conv_tc3_col_elems floats; keep it for
+ *          wgrad) and y (N, Cout, OH, OW) = col w^T + bias
+ *   dgrad  dx (N, Cin, H, W) from dy_rows (N*OH*OW, Cout) = dy with the channel axis last (maavss_nchw_to_rows) and w_perm
+ *          (Cout, KH*KW, Cin) = the tap-major copy of w (maavss_conv_tc3_permute_weights; weights are constant over a step)
+ *   wgrad  dw (Cout, Cin, KH, KW) (+)= dy_rows^T col
+ * workspace: maavss_conv_tc3_workspace_bytes(d, mode) with mode 0 fwd / 1 dgrad / 2 wgrad. */
+int maavss_conv_tc3_supported(const maavss_conv_desc* d);
+long long maavss_conv_tc3_col_elems(const maavss_conv_desc* d);
+long long maavss_conv_tc3_workspace_bytes(const maavss_conv_desc* d, int mode);
+int maavss_conv_tc3_fwd(const maavss_conv_desc* d, const float* x, const float* w, const float* bias, float* y, float* col, void* workspace,
+                        long long workspace_bytes, void* stream);
+int maavss_conv_tc3_permute_weights(const maavss_conv_desc* d, const float* w, float* w_perm, void* stream);
+int maavss_conv_tc3_dgrad(const maavss_conv_desc* d, const float* dy_rows, const float* w_perm, float* dx, void* workspace,
+                          long long workspace_bytes, void* stream);
+int maavss_conv_tc3_wgrad(const maavss_conv_desc* d, const float* col, const float* dy_rows, float* dw, int accumulate, void* workspace,
+                          long long workspace_bytes, void* stream);
+/* out[(n * inner + q) * C + c] = in[(n * C + c) * inner + q]   (channels-first -> one row of C channels per position) */
+int maavss_nchw_to_rows(const float* in, int N, int C, long long inner, float* out, void* stream);
 /* out[c] (+)= sum_{n,i} x[n, c, i]   (bias gradients). workspace: maavss_reduce_workspace_bytes(C). */
 int maavss_channel_sum(const float* x, int N, int C, long long inner, float* out, int accumulate, void* workspace, void* stream);
 int maavss_reduce_workspace_bytes(int C);
@@ -356,6 +378,14 @@ long long maavss_gemm_tf32x3_workspace_bytes(int P, int Q, int K);
 int maavss_gemm_tf32x3(const float* A, int a_mn_major, long long lda, const float* B, int b_mn_major, long long ldb, int P, int Q,
                        int K, float* out, long long ldc, int out_transposed, const float* bias, int bias_on_q, int act, float slope,
                        int accumulate, void* workspace, long long workspace_bytes, void* stream);
+/* The same product with the transposed output written in blocks of p_block rows of p (p_block % 32 == 0):
+ *   out[(p / p_block) * p_block_stride + q * ldc + p % p_block]
+ * -- with p = (sample, position), p_block = positions per sample, ldc = p_block, p_block_stride = channels * p_block this is a
+ * convolution output in NCHW straight from the GEMM over im2col rows (conv_tc3.cu). */
+int maavss_gemm_tf32x3_blocked(const float* A, int a_mn_major, long long lda, const float* B, int b_mn_major, long long ldb, int P, int Q,
+                               int K, float* out, long long ldc, int out_transposed, int p_block, long long p_block_stride,
+                               const float* bias, int bias_on_q, int act, float slope, int accumulate, void* workspace,
+                               long long workspace_bytes, void* stream);
 /* out[c] (+)= sum_r x[r * cols + c]   (bias gradient of a Linear layer from its (rows, cols) output gradient). */
 int maavss_colsum(const float* x, int rows, long long cols, float* out, int accumulate, void* stream);
 

@@ -69,7 +69,9 @@ __global__ void __launch_bounds__(256) adam_kernel(float4* __restrict__ p, const
     const float step_size = st->step_size, inv_bc2_sqrt = st->inv_bc2_sqrt;
     float4* gw = const_cast<float4*>(g);
     for (long long q = (long long)blockIdx.x * 256 + threadIdx.x; q < n4; q += (long long)gridDim.x * 256) {
-        float4 pp = p[q], gg = g[q], mm = m[q], vv = v[q];
+        // streaming accesses (evict-first): 32 B/param pass through once per step and must not push the activations of the
+        // concurrently running backward pass out of L2
+        float4 pp = __ldcs(p + q), gg = __ldcs(g + q), mm = __ldcs(m + q), vv = __ldcs(v + q);
         float* P = &pp.x;
         float* G = &gg.x;
         float* Mv = &mm.x;
@@ -83,10 +85,10 @@ __global__ void __launch_bounds__(256) adam_kernel(float4* __restrict__ p, const
             const float denom = sqrtf(V[c]) * inv_bc2_sqrt + eps;
             P[c] -= step_size * (Mv[c] / denom);
         }
-        p[q] = pp;
-        m[q] = mm;
-        v[q] = vv;
-        if (zero_grad) gw[q] = make_float4(0.f, 0.f, 0.f, 0.f);       // optimizer.zero_grad() fused into the same pass
+        __stcs(p + q, pp);
+        __stcs(m + q, mm);
+        __stcs(v + q, vv);
+        if (zero_grad) __stcs(gw + q, make_float4(0.f, 0.f, 0.f, 0.f));       // optimizer.zero_grad() fused into the same pass
     }
 }
 

@@ -59,6 +59,8 @@ struct Params {
     int transposed;            // 0: out[p * ldc + q]   1: out[q * ldc + p]
     float* out;
     long long ldc;
+    int pb;                    // transposed output in blocks of pb rows of p: out[(p / pb) * pb_stride + q * ldc + p % pb]  (0: plain)
+    long long pb_stride;
     float* ws;                 // splits > 1: partial tiles, (splits, rows, cols) compact in the layout of out
     const float* bias;         // fused epilogue only (splits == 1)
     int bias_on_q, act, accumulate;
@@ -100,9 +102,22 @@ __device__ __forceinline__ float act_t(float v, float slope) {
 // Transposed epilogue of one accumulator row: o[j * ld] = act(acc[j] + bias) (+ o[j * ld]), j < nq.  The lanes of a warp
 // hold consecutive rows, so every store (and accumulate load) of the warp is one 128-byte line.
 template <int BN, int ACT>
-__device__ __forceinline__ void store_col(const float (&acc)[BN], float* __restrict__ o, long long ld, int nq, float bp,
+__device__ __forceinline__ void store_col(float (&acc)[BN], float* __restrict__ o, long long ld, int nq, float bp,
                                           const float* __restrict__ bq, float slope, bool accum) {
-    if (nq == BN && !accum && !bq) {
+    if (bq) {
+        // per-column bias first, 16 loads in flight: a load between two stores of the loop below waits out its full latency
+        // behind the store (measured: 32 x ~350 cycles per tile on the convolution output path)
+#pragma unroll
+        for (int j0 = 0; j0 < BN; j0 += 16) {
+            float t[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) t[j] = (j0 + j < nq) ? __ldg(bq + j0 + j) : 0.f;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) acc[j0 + j] += t[j];
+        }
+        bq = nullptr;
+    }
+    if (nq == BN && !accum) {
 #pragma unroll
         for (int j = 0; j < BN; ++j) o[(size_t)j * ld] = act_t<ACT>(acc[j] + bp, slope);
         return;
@@ -117,14 +132,59 @@ __device__ __forceinline__ void store_col(const float (&acc)[BN], float* __restr
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
             if (j0 + j < nq) {
-                float v = acc[j0 + j] + bp;
-                if (bq) v += __ldg(bq + j0 + j);
-                v = act_t<ACT>(v, slope);
+                float v = act_t<ACT>(acc[j0 + j] + bp, slope);
                 if (accum) v += old[j];
                 o[(size_t)(j0 + j) * ld] = v;
             }
         }
     }
+}
+
+// Row-major epilogue of one 32 x 32 block after its transpose through shared memory: lane (sub = lane / 8, chunk = lane % 8)
+// stores the float4 of rows sub, sub + 4, ... (st = stage + sub * 32; rows_left = P - first row).
+// MODE 0: plain store   1: accumulate into the output   2: bias (per column bq4 / per row bp) + activation (+ accumulate)
+template <int MODE>
+__device__ __forceinline__ void store_rows(const float* __restrict__ st, int lane, float* __restrict__ o, long long ld, int rows_left,
+                                           const float* __restrict__ bq4, const float* __restrict__ bp, int act_acc, float slope) {
+    const int ch = lane & 7, sub = lane >> 3;
+    float4 v[8];
+#pragma unroll
+    for (int ps = 0; ps < 8; ++ps) {
+        const int rr = ps * 4 + sub;
+        v[ps] = *reinterpret_cast<const float4*>(&st[ps * 128 + ((ch ^ (rr & 7)) << 2)]);
+    }
+    if (MODE == 1 || (MODE == 2 && (act_acc & 256))) {
+        float4 old[8];
+#pragma unroll
+        for (int ps = 0; ps < 8; ++ps)                // all 8 loads in flight before the first store
+            old[ps] = (4 * ps < rows_left) ? *reinterpret_cast<const float4*>(o + (size_t)(4 * ps) * ld) : make_float4(0.f, 0.f, 0.f, 0.f);
+        if (MODE == 2) {
+            const int act = act_acc & 255;
+            float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (bq4) b4 = __ldg(reinterpret_cast<const float4*>(bq4));
+#pragma unroll
+            for (int ps = 0; ps < 8; ++ps) {
+                const float b = (bp && 4 * ps < rows_left) ? __ldg(bp + 4 * ps) : 0.f;
+                v[ps].x = apply_act(v[ps].x + b4.x + b, act, slope); v[ps].y = apply_act(v[ps].y + b4.y + b, act, slope);
+                v[ps].z = apply_act(v[ps].z + b4.z + b, act, slope); v[ps].w = apply_act(v[ps].w + b4.w + b, act, slope);
+            }
+        }
+#pragma unroll
+        for (int ps = 0; ps < 8; ++ps) { v[ps].x += old[ps].x; v[ps].y += old[ps].y; v[ps].z += old[ps].z; v[ps].w += old[ps].w; }
+    } else if (MODE == 2) {
+        const int act = act_acc & 255;
+        float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (bq4) b4 = __ldg(reinterpret_cast<const float4*>(bq4));
+#pragma unroll
+        for (int ps = 0; ps < 8; ++ps) {
+            const float b = (bp && 4 * ps < rows_left) ? __ldg(bp + 4 * ps) : 0.f;
+            v[ps].x = apply_act(v[ps].x + b4.x + b, act, slope); v[ps].y = apply_act(v[ps].y + b4.y + b, act, slope);
+            v[ps].z = apply_act(v[ps].z + b4.z + b, act, slope); v[ps].w = apply_act(v[ps].w + b4.w + b, act, slope);
+        }
+    }
+#pragma unroll
+    for (int ps = 0; ps < 8; ++ps)
+        if (4 * ps < rows_left) *reinterpret_cast<float4*>(o + (size_t)(4 * ps) * ld) = v[ps];
 }
 
 template <int BN>
@@ -341,12 +401,14 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32x3_kernel(const __grid_co
                 tc::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) tc::mbar_arrive(&tempty[a]);
+                if (p.trace && blockIdx.x == 0 && ew == 0 && lane == 0 && it < 48) p.trace[it * 8 + 6] = clock64();
             }
             if (p.transposed) {
                 // out[q * ld + p]: for one q the 32 lanes hold 32 consecutive p -> one 128-byte line per store
                 const int nq = min(32, p.Q - n0);
                 if (prow < p.P && nq > 0) {
                     float* o = dst + (size_t)n0 * ld + prow;
+                    if (fused && p.pb) o = dst + (size_t)(prow / p.pb) * p.pb_stride + (size_t)n0 * ld + prow % p.pb;
                     const float bp = (fused && p.bias && !p.bias_on_q) ? __ldg(p.bias + prow) : 0.f;
                     const float* bq = (fused && p.bias && p.bias_on_q) ? p.bias + n0 : nullptr;
                     const int act = fused ? p.act : MAAVSS_ACT_NONE;
@@ -367,36 +429,22 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32x3_kernel(const __grid_co
                 __syncwarp();
                 const int col = n0 + cc;
                 if (col < p.Q) {                         // Q % 4 == 0: the float4 is entirely inside or outside
-                    float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (fused && p.bias && p.bias_on_q) b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
                     const int row0 = m0 + q * 32 + sub;
                     float* o = dst + (size_t)row0 * ld + col;
-                    float4 old[8];
-                    if (fused && p.accumulate) {         // all 8 loads in flight before the first store
-#pragma unroll
-                        for (int ps = 0; ps < 8; ++ps)
-                            old[ps] = (row0 + 4 * ps < p.P) ? *reinterpret_cast<const float4*>(o + (size_t)(4 * ps) * ld) : make_float4(0.f, 0.f, 0.f, 0.f);
-                    }
-#pragma unroll
-                    for (int ps = 0; ps < 8; ++ps) {
-                        const int rr = ps * 4 + sub;
-                        if (row0 + 4 * ps < p.P) {
-                            float4 v = *reinterpret_cast<const float4*>(&stage[rr * 32 + (((lane & 7) ^ (rr & 7)) << 2)]);
-                            if (fused) {
-                                const float bp = (p.bias && !p.bias_on_q) ? __ldg(p.bias + row0 + 4 * ps) : 0.f;
-                                v.x += b4.x + bp; v.y += b4.y + bp; v.z += b4.z + bp; v.w += b4.w + bp;
-                                if (p.act != MAAVSS_ACT_NONE) {
-                                    v.x = apply_act(v.x, p.act, p.slope); v.y = apply_act(v.y, p.act, p.slope);
-                                    v.z = apply_act(v.z, p.act, p.slope); v.w = apply_act(v.w, p.act, p.slope);
-                                }
-                                if (p.accumulate) { v.x += old[ps].x; v.y += old[ps].y; v.z += old[ps].z; v.w += old[ps].w; }
-                            }
-                            *reinterpret_cast<float4*>(o + (size_t)(4 * ps) * ld) = v;
-                        }
-                    }
+                    const float* st = stage + sub * 32;
+                    // three specialisations: the general one carries ~200 (mostly predicated-off) instructions per stored
+                    // float4 -- measured 5800 cycles per tile on the convolution data-gradient product, which has none of it
+                    if (!fused || (!p.bias && p.act == MAAVSS_ACT_NONE && !p.accumulate))
+                        store_rows<0>(st, lane, o, ld, p.P - row0, nullptr, nullptr, 0, 0.f);
+                    else if (!p.bias && p.act == MAAVSS_ACT_NONE)
+                        store_rows<1>(st, lane, o, ld, p.P - row0, nullptr, nullptr, 0, 0.f);
+                    else
+                        store_rows<2>(st, lane, o, ld, p.P - row0, p.bias_on_q ? p.bias + col : nullptr, p.bias_on_q ? nullptr : p.bias + row0,
+                                      p.act | (p.accumulate ? 256 : 0), p.slope);
                 }
                 __syncwarp();
             }
+            if (p.trace && blockIdx.x == 0 && ew == 0 && lane == 0 && it - 1 < 48) p.trace[(it - 1) * 8 + 7] = clock64();
         }
     }
     tc::tc_fence_before();
@@ -407,7 +455,8 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32x3_kernel(const __grid_co
 // out = act(sum_s ws[s] + bias) (+ out), element order of `out` (rows x cols with pitch ldc)
 __global__ void __launch_bounds__(256) finalize_kernel(const float* __restrict__ ws, int splits, long long rows, long long cols,
                                                        float* __restrict__ out, long long ldc, const float* __restrict__ bias,
-                                                       int bias_on_cols, int act, float slope, int accumulate) {
+                                                       int bias_on_cols, int act, float slope, int accumulate, int pb,
+                                                       long long pb_stride) {
     const long long n = rows * cols;
     for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
         const long long r = i / cols, c = i - r * cols;
@@ -422,7 +471,7 @@ __global__ void __launch_bounds__(256) finalize_kernel(const float* __restrict__
         float v = ((v8[0] + v8[1]) + (v8[2] + v8[3])) + ((v8[4] + v8[5]) + (v8[6] + v8[7]));
         if (bias) v += __ldg(bias + (bias_on_cols ? c : r));
         v = apply_act(v, act, slope);
-        float* o = out + r * ldc + c;
+        float* o = pb ? out + (c / pb) * pb_stride + r * ldc + c % pb : out + r * ldc + c;
         *o = accumulate ? *o + v : v;
     }
 }
@@ -482,7 +531,17 @@ extern "C" int maavss_gemm_tf32x3(const float* A, int a_mn_major, long long lda,
                                   int P, int Q, int K, float* out, long long ldc, int out_transposed, const float* bias,
                                   int bias_on_q, int act, float slope, int accumulate, void* workspace,
                                   long long workspace_bytes, void* stream) {
+    return maavss_gemm_tf32x3_blocked(A, a_mn_major, lda, B, b_mn_major, ldb, P, Q, K, out, ldc, out_transposed, 0, 0, bias, bias_on_q, act,
+                                      slope, accumulate, workspace, workspace_bytes, stream);
+}
+
+extern "C" int maavss_gemm_tf32x3_blocked(const float* A, int a_mn_major, long long lda, const float* B, int b_mn_major, long long ldb,
+                                          int P, int Q, int K, float* out, long long ldc, int out_transposed, int p_block,
+                                          long long p_block_stride, const float* bias, int bias_on_q, int act, float slope,
+                                          int accumulate, void* workspace, long long workspace_bytes, void* stream) {
     if (P == 0 || Q == 0) return MAAVSS_OK;
+    MAAVSS_CHECK_ARG(p_block == 0 || (out_transposed && p_block % 32 == 0 && p_block > 0),
+                     "gemm_tf32x3_blocked: p_block must be a multiple of 32 and needs the transposed output");
     MAAVSS_CHECK_ARG(A && B && out && K > 0, "gemm_tf32x3: bad argument");
     MAAVSS_CHECK_ARG(maavss_gemm_tf32x3_supported(P, Q, K, a_mn_major, lda, b_mn_major, ldb, ldc, out_transposed),
                      "gemm_tf32x3: pitches must be multiples of 4 floats (and Q, ldc for a row-major output)");
@@ -500,6 +559,7 @@ extern "C" int maavss_gemm_tf32x3(const float* A, int a_mn_major, long long lda,
     p.splits = tg3::choose_splits(P, Q, K, BN);
     p.transposed = out_transposed ? 1 : 0;
     p.out = out; p.ldc = ldc;
+    p.pb = p_block; p.pb_stride = p_block_stride;
     p.bias = bias; p.bias_on_q = bias_on_q; p.act = act; p.slope = slope; p.accumulate = accumulate;
     if (const char* e = getenv("MAAVSS_G3_DBG")) p.dbg = atoi(e);
     static long long* trace_buf = nullptr;
@@ -521,10 +581,12 @@ extern "C" int maavss_gemm_tf32x3(const float* A, int a_mn_major, long long lda,
         cudaStreamSynchronize(st);
         cudaMemcpy(h, p.trace, sizeof(h), cudaMemcpyDeviceToHost);
         long long t0 = h[0];
-        fprintf(stderr, "stage: prod_empty_seen prod_tma_issued | split_full_seen split_arrived | mma_ready_seen mma_committed   (cycles since first)\n");
-        for (int i = 0; i < 40; ++i)
-            fprintf(stderr, "%3d: %7lld %7lld | %7lld %7lld | %7lld %7lld\n", i, h[i * 8] - t0, h[i * 8 + 1] - t0, h[i * 8 + 2] - t0, h[i * 8 + 3] - t0,
-                    h[i * 8 + 4] - t0, h[i * 8 + 5] - t0);
+        fprintf(stderr, "stage: prod_empty_seen prod_tma_issued | split_full_seen split_arrived | mma_ready_seen mma_committed | (per chunk) epi_drained tile_stored   (cycles since first)\n");
+        for (int i = 0; i < 40; ++i) {
+            if (!h[i * 8] && !h[i * 8 + 6]) continue;
+            fprintf(stderr, "%3d: %7lld %7lld | %7lld %7lld | %7lld %7lld | %7lld %7lld\n", i, h[i * 8] - t0, h[i * 8 + 1] - t0, h[i * 8 + 2] - t0,
+                    h[i * 8 + 3] - t0, h[i * 8 + 4] - t0, h[i * 8 + 5] - t0, h[i * 8 + 6] ? h[i * 8 + 6] - t0 : 0, h[i * 8 + 7] ? h[i * 8 + 7] - t0 : 0);
+        }
     }
     if (p.splits > 1) {
         const long long rows = out_transposed ? Q : P, cols = out_transposed ? P : Q;
@@ -532,7 +594,7 @@ extern "C" int maavss_gemm_tf32x3(const float* A, int a_mn_major, long long lda,
         const int bias_on_cols = out_transposed ? !bias_on_q : bias_on_q;
         int blocks = (int)((rows * cols + 255) / 256);       // one element per thread while the grid fits: the sum is a latency chain
         if (blocks > 148 * 8) blocks = 148 * 8;
-        tg3::finalize_kernel<<<blocks, 256, 0, st>>>(p.ws, p.splits, rows, cols, out, ldc, bias, bias_on_cols, act, slope, accumulate);
+        tg3::finalize_kernel<<<blocks, 256, 0, st>>>(p.ws, p.splits, rows, cols, out, ldc, bias, bias_on_cols, act, slope, accumulate, p.pb, p.pb_stride);
         MAAVSS_LAUNCH_CHECK();
     }
     return MAAVSS_OK;

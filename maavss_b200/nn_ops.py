@@ -6,6 +6,7 @@ existing ``param.grad`` (the flat gradient arena of optim.FlatParams) -- the gra
 train.py:158 is fused into the weight-gradient kernels -- and a fresh tensor is returned only when there is none.
 """
 import ctypes
+import os
 
 import torch
 
@@ -32,7 +33,7 @@ _wgrad_active = set()
 
 class _WgradScope:
     def __init__(self, *tensors):
-        self.tensors, self.ctx = tensors, None
+        self.tensors, self.ctx, self.side = tensors, None, None
 
     def __enter__(self):
         if not ASYNC_WGRAD:
@@ -47,6 +48,7 @@ class _WgradScope:
             if t is not None:
                 t.record_stream(side)
         _wgrad_active.add(side)
+        self.side = side
         self.ctx = torch.cuda.stream(side)
         self.ctx.__enter__()
         return self
@@ -144,6 +146,23 @@ def _conv_wgrad_tc(desc, x5, dy5, tgt, acc):
     return True
 
 
+# fp32-accurate tensor-core path (3xTF32) for the mid / deep Conv2d layers of the fusion encoders (conv_tc3.cu): on by default,
+# results within the fp32 tolerances of the layer / model tests.
+TENSOR_CORE_CONV_FP32 = os.environ.get("MAAVSS_NO_TC3", "0") in ("", "0")
+
+
+def ctx_desc_ref(desc):
+    return ctypes.byref(desc)
+
+
+def _conv_tc3_ok(desc, x5):
+    return TENSOR_CORE_CONV_FP32 and x5.is_cuda and bool(lib().maavss_conv_tc3_supported(ctypes.byref(desc)))
+
+
+def _ws_bytes(nbytes, device):
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+
+
 class ConvFn(torch.autograd.Function):
     """nn.Conv2d / nn.Conv3d forward + backward (zero padding, no dilation / groups)."""
 
@@ -155,14 +174,36 @@ class ConvFn(torch.autograd.Function):
         out3 = tuple((x5.shape[2 + i] + 2 * p[i] - w5.shape[2 + i]) // s[i] + 1 for i in range(3))
         desc = make_conv_desc(x5.shape, w5.shape, s, p, out3)
         y = torch.empty((x5.shape[0], w5.shape[0]) + out3, device=x.device, dtype=torch.float32)
-        if bias is not None or not _conv_tc(desc, 0, x5, w5.contiguous(), y):
+        col = None
+        if bias is None and _conv_tc(desc, 0, x5, w5.contiguous(), y):
+            pass                                   # opt-in bf16 tensor-core path (TENSOR_CORE_CONV) takes the layers it supports
+        elif _conv_tc3_ok(desc, x5):
+            L = lib()
+            col = torch.empty(L.maavss_conv_tc3_col_elems(ctypes.byref(desc)), device=x.device, dtype=torch.float32)
+            nb = L.maavss_conv_tc3_workspace_bytes(ctypes.byref(desc), 0)
+            ws = _ws_bytes(nb, x.device)
+            check(L.maavss_conv_tc3_fwd(ctypes.byref(desc), fptr(x5), fptr(w5.contiguous()), _opt(bias), fptr(y), fptr(col), dptr(ws),
+                                        ctypes.c_longlong(ws.numel()), stream_ptr()))
+        else:
             check(lib().maavss_conv_fwd(ctypes.byref(desc), fptr(x5), fptr(w5.contiguous()), _opt(bias), fptr(y), stream_ptr()))
         ctx.desc, ctx.nd = desc, nd
-        ctx.save_for_backward(x5, weight, bias)
+        ctx.tc3 = col is not None
+        if col is not None:
+            # tap-major copy of the weights for the data-gradient product: off the forward chain (companion stream)
+            w_perm = torch.empty_like(w5, memory_format=torch.contiguous_format)
+            scope = _WgradScope(w_perm)
+            with scope:
+                check(lib().maavss_conv_tc3_permute_weights(ctx_desc_ref(desc), fptr(w5.contiguous()), fptr(w_perm), stream_ptr()))
+            ctx.perm_stream = scope.side
+            ctx.save_for_backward(x5, weight, bias, col, w_perm)
+        else:
+            ctx.save_for_backward(x5, weight, bias)
         return y if nd == 5 else y.squeeze(2)
 
     @staticmethod
     def backward(ctx, dy):
+        if ctx.tc3:
+            return ConvFn._backward_tc3(ctx, dy)
         x5, weight, bias = ctx.saved_tensors
         dy5 = _as5(dy.contiguous())
         desc = ctx.desc
@@ -181,6 +222,40 @@ class ConvFn(torch.autograd.Function):
                 if tgt is not None:
                     channel_sum(dy5, tgt, acc)
         return dx, gw, gb, None, None
+
+
+def _conv_backward_tc3(ctx, dy):
+    """Backward of a layer whose forward ran on conv_tc3: dy with the channel axis last feeds both GEMMs."""
+    x5, weight, bias, col, w_perm = ctx.saved_tensors
+    if ctx.perm_stream is not None:
+        torch.cuda.current_stream().wait_stream(ctx.perm_stream)
+    dy5 = _as5(dy.contiguous())
+    desc, L, dev = ctx.desc, lib(), dy.device
+    N, Cout = dy5.shape[0], dy5.shape[1]
+    inner = dy5[0, 0].numel()
+    dx = gw = gb = None
+    dy_rows = torch.empty(N * inner, Cout, device=dev, dtype=torch.float32)
+    check(L.maavss_nchw_to_rows(fptr(dy5), N, Cout, inner, fptr(dy_rows), stream_ptr()))
+    if ctx.needs_input_grad[0]:
+        dx5 = torch.empty_like(x5)
+        ws = _ws_bytes(L.maavss_conv_tc3_workspace_bytes(ctypes.byref(desc), 1), dev)
+        check(L.maavss_conv_tc3_dgrad(ctypes.byref(desc), fptr(dy_rows), fptr(w_perm), fptr(dx5), dptr(ws), ctypes.c_longlong(ws.numel()),
+                                      stream_ptr()))
+        dx = dx5 if ctx.nd == 5 else dx5.squeeze(2)
+    with _WgradScope(dy5, dy_rows, col):
+        tgt, acc, gw = _grad_slot(weight, ctx.needs_input_grad[1])
+        if tgt is not None:
+            ws2 = _ws_bytes(L.maavss_conv_tc3_workspace_bytes(ctypes.byref(desc), 2), dev)
+            check(L.maavss_conv_tc3_wgrad(ctypes.byref(desc), fptr(col), fptr(dy_rows), fptr(tgt), acc, dptr(ws2),
+                                          ctypes.c_longlong(ws2.numel()), stream_ptr()))
+        if bias is not None:
+            tgt, acc, gb = _grad_slot(bias, ctx.needs_input_grad[2])
+            if tgt is not None:
+                channel_sum(dy5, tgt, acc)
+    return dx, gw, gb, None, None
+
+
+ConvFn._backward_tc3 = staticmethod(_conv_backward_tc3)
 
 
 class ConvTransposeFn(torch.autograd.Function):

@@ -129,7 +129,9 @@ def allreduce_gradients(optimizer):
 
 # CTAs of the early Adam pass: it streams ~1 GB next to the latency-bound encoder backward and must not take its SM slots
 EARLY_ADAM_CTAS = int(os.environ.get("MAAVSS_EARLY_ADAM_CTAS", "148"))
-EARLY_ADAM = os.environ.get("MAAVSS_EARLY_ADAM", "1") != "0"
+# Off by default: with the encoder convolutions on the tensor-core path the backward pass lives on L2-resident im2col
+# matrices, and a 1.2 GB optimizer stream next to it costs more (2.44 ms/step) than running Adam after it (2.32 ms).
+EARLY_ADAM = os.environ.get("MAAVSS_EARLY_ADAM", "0") != "0"
 
 
 class EarlyGradAllReduce:

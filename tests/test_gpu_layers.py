@@ -66,6 +66,58 @@ def test_conv2d(cin, cout, k, s, p, hw, B, bias):
     assert rel_err(ours.weight.grad, 2 * ref.weight.grad) < 1e-5
 
 
+# the mid / deep encoder layers of avse_model.AV_Fusion_Model at the headline batch (16 clips x 4 stacked windows): these run on
+# the 3xTF32 tensor-core path (conv_tc3.cu); checked against torch fp32 AND against the SIMT kernels they replace
+TC3_CASES = [
+    (16, 32, (1, 9), (1, 2), (0, 4), (8, 256), 64),
+    (64, 64, (1, 9), (1, 2), (0, 4), (8, 32), 64),
+    (64, 64, (1, 9), (1, 2), (0, 4), (8, 8), 64),
+    (8, 32, (5, 5), (2, 2), (2, 2), (32, 64), 64),
+    (32, 64, (5, 5), (2, 2), (2, 2), (16, 32), 64),
+    (64, 64, (5, 5), (1, 2), (2, 2), (8, 8), 64),
+    (8, 16, (3, 9), (2, 2), (1, 4), (32, 64), 6),          # avse_model_conv / avse_model_final style kernel, ragged batch
+]
+
+
+@pytest.mark.parametrize("cin,cout,k,s,p,hw,B", TC3_CASES)
+def test_conv2d_tensor_core_fp32(cin, cout, k, s, p, hw, B):
+    import ctypes
+    from maavss_b200 import layers as L
+    from maavss_b200 import nn_ops as ops
+    from maavss_b200._lib import lib
+    oh, ow = (hw[0] + 2 * p[0] - k[0]) // s[0] + 1, (hw[1] + 2 * p[1] - k[1]) // s[1] + 1
+    desc = ops.make_conv_desc((B, cin, 1, *hw), (cout, cin, 1, *k), (1, *s), (0, *p), (1, oh, ow))
+    assert lib().maavss_conv_tc3_supported(ctypes.byref(desc)) == 1
+    torch.manual_seed(3)
+    ref = nn.Conv2d(cin, cout, k, s, p, bias=True)
+    ours, ref = pair(L.Conv2d(cin, cout, k, s, p, bias=True), ref)
+    x = torch.randn(B, cin, *hw, generator=g(12)).cuda()
+    dy = torch.randn(B, cout, oh, ow, generator=g(13)).cuda()
+    res = {}
+    for tc in (True, False):
+        ops.TENSOR_CORE_CONV_FP32 = tc
+        try:
+            ours.zero_grad(set_to_none=True)
+            xo = x.clone().requires_grad_()
+            yo = ours(xo)
+            yo.backward(dy)
+            yo2 = ours(xo)                 # second pass accumulates into the existing .grad
+            yo2.backward(dy)
+            res[tc] = (yo.detach(), xo.grad.clone(), ours.weight.grad.clone(), ours.bias.grad.clone())
+        finally:
+            ops.TENSOR_CORE_CONV_FP32 = True
+    xr = x.clone().requires_grad_()
+    yr = ref(xr)
+    yr.backward(dy)
+    for tc in (True, False):
+        y, dx, dw, db = res[tc]
+        assert rel_err(y, yr) < 3e-6
+        assert rel_err(dx, 2 * xr.grad) < 3e-6
+        assert rel_err(dw, 2 * ref.weight.grad) < 1e-5
+        assert rel_err(db, 2 * ref.bias.grad) < 1e-5
+    assert rel_err(res[True][0], res[False][0]) < 3e-6
+
+
 def test_conv3d():
     from maavss_b200 import layers as L
     torch.manual_seed(1)

@@ -193,7 +193,13 @@ def test_batched_windows_equal_sequential():
     mods = dict(m0.named_modules())
     noisy = np.array([k.endswith(".bias") and type(mods[k.rsplit(".", 1)[0]]).__name__.startswith("Conv") for k in names])
     nm = np.array(names)
-    assert_digest_close(nm[~noisy], p1[~noisy], p0[~noisy], 1e-5, 1e-7)
+    # sampled entries tight.  The per-tensor sums (column 0) collect the entries whose gradient is rounding noise -- Adam moves
+    # them a full +-lr whatever the magnitude, and the batch-2 and batch-8 passes use different kernels for some layers (the
+    # tensor-core convolutions need >= 128 positions) -- so they are held to 1e-4 of the largest possible drift 2 steps x lr x numel
+    assert_digest_close(nm[~noisy], p1[~noisy], p0[~noisy], 1e-5, 1e-7, slice(1, None))
+    numel = {k: p.numel() for k, p in m0.named_parameters()}
+    for k, a, b in zip(nm[~noisy], p1[~noisy][:, 0], p0[~noisy][:, 0]):
+        assert abs(a - b) <= 1e-5 * abs(b) + 1e-4 * 2 * 1e-5 * numel[k] + 1e-7, (k, a, b)
     assert_digest_close(nm[noisy], p1[noisy], p0[noisy], 0, 2.5e-5, slice(1, None))      # zero-gradient conv biases: Adam on noise
     # running_var = E[x^2] - mean^2 amplifies the ~1e-7 summation-order differences between the batch-2 and batch-8
     # split-reduction convolutions when mean^2 >> var (the phasegram encoder's first layers): 1e-3 here, 1e-5 vs the goldens
