@@ -111,7 +111,7 @@ int maavss_conv_wgrad_tc(const maavss_conv_desc* d, const float* x, const float*
                          long long workspace_bytes, void* stream);
 /* fp32-accurate tensor-core path (3xTF32 on tcgen05, tc_gemm3.cu) for the mid / deep Conv2d layers of the fusion encoders
  * (avse_model.py:427-446,474-502; avse_model_conv.py:427-500): same products as maavss_conv_fwd / _dgrad / _wgrad, <= 5e-6 of
- * torch fp32.  supported(): 2-D layers (D = KD = 1) with Cin >= 8, Cout >= 16 and a multiple of 4, Cin*KH*KW a multiple of 4,
+ * torch fp32.  supported(): 2-D layers (D = KD = 1) with Cin >= 16 (or Cin >= 8 and Cout >= 32), Cout a multiple of 4, Cin*KH*KW a multiple of 4,
  * OH*OW a multiple of 32, N*OH*OW >= 128 and an im2col matrix of <= 512 MB.
  *   fwd    writes the im2col matrix col (N*OH*OW, Cin*KH*KW) (caller-owned, maavss_conv_tc3_col_elems floats; keep it for
  *          wgrad) and y (N, Cout, OH, OW) = col w^T + bias

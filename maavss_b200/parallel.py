@@ -127,60 +127,74 @@ def allreduce_gradients(optimizer):
     optimizer.grad_scale = 1.0 / _WORLD
 
 
-# CTAs of the early Adam pass: it streams ~1 GB next to the latency-bound encoder backward and must not take its SM slots
-EARLY_ADAM_CTAS = int(os.environ.get("MAAVSS_EARLY_ADAM_CTAS", "148"))
-# Off by default: with the encoder convolutions on the tensor-core path the backward pass lives on L2-resident im2col
-# matrices, and a 1.2 GB optimizer stream next to it costs more (2.44 ms/step) than running Adam after it (2.32 ms).
-EARLY_ADAM = os.environ.get("MAAVSS_EARLY_ADAM", "0") != "0"
+# CTAs of the early Adam pass (0 = the kernel's own grid): 2 per SM measured best beside the LSTM backward (2.21 vs 2.25 ms/step)
+EARLY_ADAM_CTAS = int(os.environ.get("MAAVSS_EARLY_ADAM_CTAS", "296"))
+EARLY_ADAM = os.environ.get("MAAVSS_EARLY_ADAM", "1") != "0"
 
 
 class EarlyGradAllReduce:
     """Take the tail of the optimizer step off the critical path.
 
-    The flat arenas are split at `offset`: everything from `offset` on (the LSTM / fc / head weights of the fusion models,
-    98 % of the parameters, whose gradients are final once the LSTM backward has run) is handled on a side stream as soon
-    as `start()` is called from an autograd hook, while the convolutional encoders are still back-propagating on the main
-    stream: the data-parallel all-reduce of that part of the gradient arena (N > 1), then -- `early_adam` -- its Adam
-    update and zero_grad.  No kernel of the remaining backward pass reads those parameters (the encoders sit in front of
-    the LSTM).  `finish()` is the rest of the optimizer step: exchange + Adam + zero_grad of the head, joined with the
-    side stream.  Both streams' work is captured when the step is recorded into a CUDA graph."""
+    The flat arenas of the fusion model are [encoders | lstm | fc1 fc2 (decoders: unused) a_fc1 v_fc1].  Two hooks of the
+    backward pass hand pieces of the arena to a side stream:
 
-    def __init__(self, optimizer, offset, early_adam=True):
+    * `start_heads()`, when the gradient of the LSTM OUTPUT exists: the gradients from `head_offset` (first fc1 weight) on
+      -- 90 % of all parameters -- are final and no later kernel reads those weights.  They are all-reduced (N > 1) and,
+      with `early_adam`, Adam-updated and zeroed right away: the 1.1 GB optimizer stream then runs beside the LSTM
+      backward, which is 8 small latency-bound launches per direction and leaves HBM idle.  (Placed any later it runs
+      beside the encoder backward, whose im2col matrices live in L2: measured slower than not overlapping at all.)
+    * `start()`, when the gradient of the LSTM INPUT exists: the LSTM weights' gradients [offset, head_offset) are
+      all-reduced (N > 1) while the encoders back-propagate.
+
+    `finish()` is the rest of the optimizer step: exchange of what is left, Adam + zero_grad of what is left, joined with
+    the side stream.  Everything is captured when the step is recorded into a CUDA graph."""
+
+    def __init__(self, optimizer, offset, early_adam=True, head_offset=None):
         self.opt, self.offset, self.early_adam = optimizer, int(offset), early_adam and EARLY_ADAM
+        self.head_offset = int(head_offset) if head_offset is not None else None
         self.side = torch.cuda.Stream()
-        self.started = False
+        self.started = self.heads_started = False
         if _GROUP is not None:
             optimizer.grad_scale = 1.0 / _WORLD
 
-    def start(self):
-        if self.started:
-            return
-        self.started = True
+    def _fork(self):
         self.side.wait_stream(torch.cuda.current_stream())
-        nn_ops.join_wgrad_streams(target=self.side, clear=False)      # the tail's weight gradients may still be in flight
+        nn_ops.join_wgrad_streams(target=self.side, clear=False)      # this part's weight gradients may still be in flight
+
+    def start_heads(self):
+        if self.heads_started or self.head_offset is None or (_GROUP is None and not self.early_adam):
+            return
+        self.heads_started = True
+        self._fork()
         with torch.cuda.stream(self.side):
             if _GROUP is not None:
-                allreduce_sum_(self.opt.flat.grad[self.offset:])
+                allreduce_sum_(self.opt.flat.grad[self.head_offset:])
             if self.early_adam:
                 self.opt.prepare()
-                self.opt.apply_range(self.offset, None, zero_grad=True, max_ctas=EARLY_ADAM_CTAS)
+                self.opt.apply_range(self.head_offset, None, zero_grad=True, max_ctas=EARLY_ADAM_CTAS)
+
+    def start(self):
+        if self.started or _GROUP is None:
+            return
+        self.started = True
+        self._fork()
+        with torch.cuda.stream(self.side):
+            allreduce_sum_(self.opt.flat.grad[self.offset:self.head_offset if self.heads_started else None])
 
     def finish(self):
-        """Everything of optimizer.step(); optimizer.zero_grad() (and the gradient exchange) that start() has not done."""
+        """Everything of optimizer.step(); optimizer.zero_grad() (and the gradient exchange) that the hooks have not done."""
         opt, g = self.opt, self.opt.flat.grad
-        if self.started:
-            if _GROUP is not None and self.offset > 0:
-                allreduce_sum_(g[:self.offset])
+        if _GROUP is not None:
+            left = self.offset if self.started else (self.head_offset if self.heads_started else g.numel())
+            if left > 0:
+                allreduce_sum_(g[:left])
+        if self.started or self.heads_started:
             torch.cuda.current_stream().wait_stream(self.side)
-            if self.early_adam:
-                opt.apply_range(0, self.offset, zero_grad=True)
-            else:
-                opt.step_and_zero_grad()
+        if self.heads_started and self.early_adam:
+            opt.apply_range(0, self.head_offset, zero_grad=True)
         else:
-            if _GROUP is not None:
-                allreduce_sum_(g)
             opt.step_and_zero_grad()
-        self.started = False
+        self.started = self.heads_started = False
 
 
 def allreduce_max_(t):

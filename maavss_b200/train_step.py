@@ -113,24 +113,35 @@ class FusionTrainStep(_TrainStepBase):
         self._setup_early_allreduce(overlap_allreduce)
 
     def _setup_early_allreduce(self, enabled):
-        """avse_model.AV_Fusion_Model.forward trains [encoders | lstm fc1 fc2 (decoders: unused) a_fc1 v_fc1]: from the
-        first LSTM weight to the end of the arena nothing receives gradient -- and no parameter is read -- after the LSTM
-        backward, so that tail is exchanged (N > 1) and Adam-updated while the encoders back-propagate (the hook fires
-        when the LSTM's input gradient exists)."""
+        """avse_model.AV_Fusion_Model.forward trains [encoders | lstm | fc1 fc2 (decoders: unused) a_fc1 v_fc1]: the fc /
+        head part is final (gradients written, weights no longer read) once the LSTM output's gradient exists, the LSTM
+        part once the LSTM input's gradient exists; parallel.EarlyGradAllReduce takes them from there."""
         m = self.model
         if not enabled or getattr(m, "VARIANT", None) != "fc" or not self.batch_windows:
             return
         first = next(m.lstm.parameters())
+        head = next(m.fc1.parameters())
         flat = self.opt.flat
-        if id(first) not in flat.index:
+        if id(first) not in flat.index or id(head) not in flat.index:
             return
-        self.early = parallel.EarlyGradAllReduce(self.opt, flat.offsets[flat.index[id(first)]])
+        off, head_off = flat.offsets[flat.index[id(first)]], flat.offsets[flat.index[id(head)]]
+        # the claim above, checked: every parameter behind fc1 in the arena belongs to fc1 / fc2 / the heads / the unused decoders
+        tail_ok = {id(p) for mod in (m.fc1, m.fc2, m.a_fc1, m.v_fc1, m.stft_decoder, m.phasegram_decoder) for p in mod.parameters()}
+        if head_off < off or any(id(p) not in tail_ok for p, o in zip(flat.params, flat.offsets) if o >= head_off):
+            head_off = None
+        self.early = parallel.EarlyGradAllReduce(self.opt, off, head_offset=head_off)
 
         def pre_hook(mod, args):
             x = args[0]
             if torch.is_tensor(x) and x.requires_grad:
                 x.register_hook(lambda g: (self.early.start() if self._running else None, None)[1])
+
+        def post_hook(mod, args, out):
+            y = out[0] if isinstance(out, tuple) else out
+            if torch.is_tensor(y) and y.requires_grad:
+                y.register_hook(lambda g: (self.early.start_heads() if self._running else None, None)[1])
         m.lstm.register_forward_pre_hook(pre_hook)
+        m.lstm.register_forward_hook(post_hook)
 
     def _pg_kw(self):
         """Data parallel with global_phasegram: `attn` holds the frames of parallel.rolled_clip_indices (the loader applied

@@ -75,7 +75,7 @@ TC3_CASES = [
     (8, 32, (5, 5), (2, 2), (2, 2), (32, 64), 64),
     (32, 64, (5, 5), (2, 2), (2, 2), (16, 32), 64),
     (64, 64, (5, 5), (1, 2), (2, 2), (8, 8), 64),
-    (8, 16, (3, 9), (2, 2), (1, 4), (32, 64), 6),          # avse_model_conv / avse_model_final style kernel, ragged batch
+    (8, 32, (3, 9), (2, 2), (1, 4), (32, 64), 6),          # avse_model_conv / avse_model_final style kernel, ragged batch
 ]
 
 
