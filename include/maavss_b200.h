@@ -228,6 +228,16 @@ int maavss_lstm_step_fwd(const float* gin, const float* w_hh_fwd, const float* w
 int maavss_lstm_step_bwd(const float* dy, const float* gates, const float* cells, const float* w_hh_fwd, const float* w_hh_rev,
                          float* dgates, float* dcell, int B, int T, int H, int step, void* stream);
 
+/* The T recurrent steps of both directions as ONE launch (lstm_persist.cu; H = 256 as the reference builds it,
+ * avse_model.py:542): thread-block clusters of 8 CTAs per (direction, 8 batch rows) keep w_hh in registers for the whole
+ * sequence and exchange the hidden state / gate gradients through distributed shared memory.  Same arguments and results as
+ * running maavss_lstm_step_fwd / _bwd for step = 0..T-1 / T-1..0 (the backward needs no dcell buffer). */
+int maavss_bilstm_recurrent_supported(int B, int T, int H);
+int maavss_bilstm_recurrent_fwd(const float* gin, const float* w_hh_fwd, const float* w_hh_rev, float* gates, float* cells, float* y, int B,
+                                int T, int H, void* stream);
+int maavss_bilstm_recurrent_bwd(const float* dy, const float* gates, const float* cells, const float* w_hh_fwd, const float* w_hh_rev,
+                                float* dgates, int B, int T, int H, void* stream);
+
 /* The whole layer in one call (SURVEY 8b bilstm_fwd / bilstm_bwd): x (B, T, I) -> y (B, T, 2H).  gin / gates (2, B, T, 4H) and
  * cells (2, B, T, H) are outputs the backward needs (caller-owned).  The input projections and all weight / input gradients
  * run on the 3xTF32 tensor-core GEMM when B*T >= 32, the T recurrent steps are one launch each.

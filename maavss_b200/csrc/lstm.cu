@@ -2,6 +2,7 @@
 // avse_model.py:542-543, avse_model_final.py:132-133): the recurrent part, one launch per time step covering both
 // directions.  The input projections x w_ih^T and all weight gradients are GEMMs (gemm_simt.cu).
 // Layouts: gin/gates/dgates (2, B, T, 4H) with gate order i,f,g,o; cells (2, B, T, H); y/dy (B, T, 2H).
+#include <stdlib.h>
 #include "common.cuh"
 #include "../../include/maavss_b200.h"
 
@@ -222,6 +223,19 @@ __global__ void __launch_bounds__(256) lstm_hprev_kernel(const float* __restrict
 
 inline size_t al256(size_t v) { return (v + 255) & ~(size_t)255; }
 
+// one launch for all T steps (lstm_persist.cu) unless MAAVSS_LSTM_STEPS=1 asks for the per-step kernels (benchmarks)
+inline bool use_recurrent_kernel(int B, int T, int H, int backward) {
+    // bit 0: per-step kernels in the forward, bit 1: in the backward.  Default 2: measured on the headline step (same box,
+    // 150 steps each) 2.147 ms with the one-launch forward + per-step backward, 2.170 the other way round, 2.215 both in one
+    // launch, 2.240 both per step -- the one-launch backward (a full register file per CTA) cannot share SMs with the
+    // weight-gradient GEMMs and the optimizer tail that run beside it.
+    static const int steps = [] {
+        const char* e = getenv("MAAVSS_LSTM_STEPS");
+        return e ? atoi(e) : 2;
+    }();
+    return !(steps & (backward ? 2 : 1)) && maavss_bilstm_recurrent_supported(B, T, H);
+}
+
 // y[M, N] = x w^T on the 3xTF32 tensor-core GEMM when the shape allows, else the SIMT kernels
 int proj_fwd(const float* x, const float* w, float* y, int M, int N, int K, void* ws, long long ws_bytes, void* st) {
     if (M >= 32 && maavss_gemm_tf32x3_supported(N, M, K, 0, K, 0, K, N, 1) && maavss_gemm_tf32x3_workspace_bytes(N, M, K) <= ws_bytes)
@@ -263,6 +277,7 @@ extern "C" int maavss_bilstm_fwd(const float* x, const float* w_ih_fwd, const fl
     if (rc) return rc;
     rc = proj_fwd(x, w_ih_rev, gin + (size_t)M * 4 * H, M, 4 * H, I, ws, wsb, stream);
     if (rc) return rc;
+    if (use_recurrent_kernel(B, T, H, 0)) return maavss_bilstm_recurrent_fwd(gin, w_hh_fwd, w_hh_rev, gates, cells, y, B, T, H, stream);
     for (int s = 0; s < T; ++s) {
         rc = maavss_lstm_step_fwd(gin, w_hh_fwd, w_hh_rev, gates, cells, y, B, T, H, s, stream);
         if (rc) return rc;
@@ -322,11 +337,16 @@ extern "C" int maavss_bilstm_bwd(const float* dy, const float* x, const float* w
     void* gws = base;
     float* dcell = (float*)(base + g);
     float* hprev = (float*)((uint8_t*)dcell + al256(sizeof(float) * 2 * (size_t)B * H));
-    MAAVSS_CUDA(cudaMemsetAsync(dcell, 0, sizeof(float) * 2 * (size_t)B * H, st));
     int rc;
-    for (int s = T - 1; s >= 0; --s) {
-        rc = maavss_lstm_step_bwd(dy, gates, cells, w_hh_fwd, w_hh_rev, dgates, dcell, B, T, H, s, stream);
+    if (use_recurrent_kernel(B, T, H, 1)) {
+        rc = maavss_bilstm_recurrent_bwd(dy, gates, cells, w_hh_fwd, w_hh_rev, dgates, B, T, H, stream);
         if (rc) return rc;
+    } else {
+        MAAVSS_CUDA(cudaMemsetAsync(dcell, 0, sizeof(float) * 2 * (size_t)B * H, st));
+        for (int s = T - 1; s >= 0; --s) {
+            rc = maavss_lstm_step_bwd(dy, gates, cells, w_hh_fwd, w_hh_rev, dgates, dcell, B, T, H, s, stream);
+            if (rc) return rc;
+        }
     }
     // the input gradient first: it is what the rest of the backward pass waits for
     const float* w_ih[2] = {w_ih_fwd, w_ih_rev};
