@@ -216,8 +216,18 @@ def algorithmic_bytes(name, a):
         w = d.Cout * d.Cin * d.KD * d.KH * d.KW
         tag = f"N{d.N} C{d.Cin}->{d.Cout} k{d.KD}x{d.KH}x{d.KW} s{d.SH}x{d.SW} in{d.D}x{d.H}x{d.W}"
         return 4 * (x + y + (2 * w if name.endswith("wgrad") else w)), tag
+    if name in ("maavss_conv_tc3_fwd", "maavss_conv_tc3_dgrad", "maavss_conv_tc3_wgrad"):
+        # the layer's algorithmic traffic (x, y, w once each), NOT the im2col matrix the path moves through L2
+        d = a[0]._obj
+        x = d.N * d.Cin * d.D * d.H * d.W
+        y = d.N * d.Cout * d.OD * d.OH * d.OW
+        w = d.Cout * d.Cin * d.KD * d.KH * d.KW
+        tag = f"N{d.N} C{d.Cin}->{d.Cout} k{d.KH}x{d.KW} s{d.SH}x{d.SW} in{d.H}x{d.W}"
+        return 4 * (x + y + (2 * w if name.endswith("wgrad") else w)), tag
     if name == "maavss_adam_step":
         return 28 * iv(a[4]), f"n{iv(a[4])}"
+    if name == "maavss_adam_apply":
+        return (32 if iv(a[11]) else 28) * iv(a[4]), f"n{iv(a[4])}"
     if name in ("maavss_bn_apply_act", "maavss_bn_bwd_apply", "maavss_bn_reduce", "maavss_bn_bwd_reduce"):
         k = {"maavss_bn_apply_act": (4, 2), "maavss_bn_bwd_apply": (6, 4), "maavss_bn_reduce": (1, 1), "maavss_bn_bwd_reduce": (4, 3)}[name]
         N, C, inner = iv(a[k[0]]), iv(a[k[0] + 1]), iv(a[k[0] + 2])

@@ -244,6 +244,35 @@ def test_lstm(B, T, I, H):
         assert rel_err(getattr(ours, n).grad.cpu().double(), getattr(ref, n).grad) < 2e-5, n
 
 
+@pytest.mark.parametrize("B,T", [(64, 8), (13, 6), (2, 3)])
+def test_lstm_recurrent_kernels(B, T):
+    """One-launch cluster kernels (lstm_persist.cu) == the per-step kernels (lstm.cu), forward and backward, through the C ABI."""
+    from maavss_b200._lib import check, fptr, lib, stream_ptr
+    L, H = lib(), 256
+    assert L.maavss_bilstm_recurrent_supported(B, T, H) == 1 and L.maavss_bilstm_recurrent_supported(B, T, 96) == 0
+    gin = torch.randn(2, B, T, 4 * H, generator=g(40)).cuda()
+    w = [(torch.randn(4 * H, H, generator=g(41 + d)) * H ** -0.5).cuda() for d in range(2)]
+    dy = torch.randn(B, T, 2 * H, generator=g(43)).cuda()
+    out = []
+    for one_launch in (False, True):
+        gates, cells = torch.empty(2, B, T, 4 * H, device="cuda"), torch.empty(2, B, T, H, device="cuda")
+        y, dgates = torch.empty(B, T, 2 * H, device="cuda"), torch.empty(2, B, T, 4 * H, device="cuda")
+        if one_launch:
+            check(L.maavss_bilstm_recurrent_fwd(fptr(gin), fptr(w[0]), fptr(w[1]), fptr(gates), fptr(cells), fptr(y), B, T, H, stream_ptr()))
+            check(L.maavss_bilstm_recurrent_bwd(fptr(dy), fptr(gates), fptr(cells), fptr(w[0]), fptr(w[1]), fptr(dgates), B, T, H, stream_ptr()))
+        else:
+            for s_ in range(T):
+                check(L.maavss_lstm_step_fwd(fptr(gin), fptr(w[0]), fptr(w[1]), fptr(gates), fptr(cells), fptr(y), B, T, H, s_, stream_ptr()))
+            dcell = torch.zeros(2, B, H, device="cuda")
+            for s_ in range(T - 1, -1, -1):
+                check(L.maavss_lstm_step_bwd(fptr(dy), fptr(gates), fptr(cells), fptr(w[0]), fptr(w[1]), fptr(dgates), fptr(dcell), B, T, H, s_,
+                                             stream_ptr()))
+        torch.cuda.synchronize()
+        out.append((gates, cells, y, dgates))
+    for a, b in zip(out[1], out[0]):
+        assert rel_err(a, b) < 2e-6
+
+
 def test_mse_and_adam():
     from maavss_b200 import nn_ops as ops
     from maavss_b200 import optim

@@ -493,6 +493,13 @@ def test_graph_step_checkpoint_roundtrip():
     # one Adam step at lr 1e-4 moves a weight by <= 1e-4; a wrong bias correction (step 1 instead of 4) changes that move by ~2x
     # (conv biases in front of a BatchNorm see Adam on rounding noise, see test_fusion_train_step_golden: skipped)
     mods = dict(m0.named_modules())
-    moved = [(p2.detach() - p0.detach()).abs().max().item() for (k, p2), (_, p0) in zip(m2.named_parameters(), m0.named_parameters())
-             if not (k.endswith(".bias") and type(mods[k.rsplit(".", 1)[0]]).__name__.startswith("Conv"))]
-    assert max(moved) < 2e-5, max(moved)
+    # A wrong step count moves (nearly) EVERY entry; what the two runs may legitimately differ in is a handful of entries whose
+    # gradient is rounding noise: the thin-layer weight gradients and the skinny-Linear data gradients meet through atomics, so
+    # their last bits depend on CTA scheduling, and Adam turns a flipped sign into a full +-lr move per step (seen: one entry of
+    # a_fc1.0.weight 1.4e-4 apart in some runs, 0 in others).  So: >= 99.9 % of every tensor within 2e-5, nothing beyond 4 steps x lr.
+    for (k, p2), (_, p0) in zip(m2.named_parameters(), m0.named_parameters()):
+        if k.endswith(".bias") and type(mods[k.rsplit(".", 1)[0]]).__name__.startswith("Conv"):
+            continue
+        d = (p2.detach() - p0.detach()).abs()
+        assert (d < 2e-5).float().mean().item() >= 0.999, (k, (d < 2e-5).float().mean().item())
+        assert d.max().item() <= 4.5e-4, (k, d.max().item())
