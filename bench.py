@@ -658,6 +658,7 @@ def run_ours(args):
             "config": config_record(world),
             "run": {"global_batch": world * B, "parallelism": f"dp{world}", "execution": "eager" if args.eager else "cuda-graph",
                     "sync_bn": world > 1, "global_phasegram_semantics": world > 1,
+                    "bn_exchange": ("nvlink peer memory kernel" if parallel.peer_exchange() is not None else "nccl") if world > 1 else None,
                     "grad_allreduce": ("overlapped with the encoder backward" if step.early is not None else "after backward") if world > 1 else None},
             "clocks": clk,
             "e2e": {"value": round(world * B * args.steps / (ms_e2e / 1e3), 2), "unit": "clips/s", "h2d_bytes_per_step": h2d,

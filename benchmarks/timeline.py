@@ -14,10 +14,15 @@ def capture(out):
     import torch
     import bench
     from maavss_b200 import av_dataset, avse_model, optim, train_step
-    dev = torch.device("cuda", 0)
+    from maavss_b200 import parallel
+    rank, world = parallel.init()              # torchrun: data-parallel step (sync-BN, gradient exchange); rank 0 writes the CSV
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
     B = bench.B_PER_GPU
     torch.manual_seed(0)
     model = avse_model.AV_Fusion_Model([B, 2, 64, 128], [B, 1, 8, 4096], 8)
+    parallel.broadcast_module(model)
     model.train()
     opt = optim.Adam(model.parameters(), lr=bench.LR)
     ds = av_dataset.AV_Dataset(num_frames=bench.CLIP_FRAMES, fft_len=bench.N_FFT, hops_per_frame=bench.HOPS_PER_FRAME,
@@ -43,6 +48,11 @@ def capture(out):
         if e.device_type is not None and "cuda" in str(e.device_type).lower():
             rows.append((e.time_range.start, e.time_range.end - e.time_range.start, getattr(e, "device_resource_id", -1), e.name))
     rows.sort()
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        if rank != 0:
+            os._exit(0)
     t0 = rows[0][0] if rows else 0
     os.makedirs(os.path.dirname(out) or ".", exist_ok=True)
     with open(out, "w") as f:
@@ -50,7 +60,9 @@ def capture(out):
         for s, d, st, n in rows:
             n = n.replace('"', "'")
             f.write(f"{s - t0:.3f},{d:.3f},{st},\"{n[:120]}\"\n")
-    print(f"{len(rows)} device records -> {out}")
+    print(f"{len(rows)} device records -> {out}", flush=True)
+    if world > 1:
+        os._exit(0)
 
 
 def view(path, which=-1):

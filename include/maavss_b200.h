@@ -453,6 +453,23 @@ int maavss_flow_pyr_lk(const unsigned char* prev_gray, const unsigned char* next
  *   allreduce_sum_f64  train-mode BatchNorm partial sums between bn_reduce and bn_apply (statistics of the global batch)
  *   allreduce_max_u32  the whole-batch max of utilities.video_phasegram (utilities.py:226-227), float bits as uint32
  * All three enqueue on `stream` (capturable into the train step's CUDA graph). */
+/* Small-message sum all-reduce over NVLink peer memory (peer_exchange.cu): the BatchNorm partial sums, 30 exchanges of <= 32 KB
+ * per optimizer step on the critical path, as ONE single-CTA kernel per rank and exchange (peer stores + flag, spin on own
+ * memory, sum in rank order: bit-identical on every rank) instead of an NCCL all-reduce each.
+ *   peer_create     allocates the rank's buffer (channels x 4 slots x 16 ranks x max_doubles doubles) and returns its 64-byte CUDA
+ *                   IPC handle; the caller gathers the handles of all ranks (any side channel)
+ *   peer_connect    opens the other ranks' buffers: handles = world x 64 bytes, indexed by rank
+ *   peer_allreduce_sum_f64   in place, n <= max_doubles, enqueued on `stream` (capturable).  Exchanges of one channel must be
+ *                   issued in the same order on every rank; streams that run concurrently use different channels.
+ *   peer_status     *error != 0 after a rank waited ~2 s for a peer and gave up (the results are then garbage, not a hang). */
+typedef struct maavss_peer maavss_peer;
+int maavss_peer_create(maavss_peer** peer, int rank, int world, int channels, int max_doubles, void* handle64);
+int maavss_peer_connect(maavss_peer* peer, const void* handles);
+int maavss_peer_capacity(const maavss_peer* peer);
+int maavss_peer_allreduce_sum_f64(maavss_peer* peer, int channel, double* data, long long n, void* stream);
+int maavss_peer_status(maavss_peer* peer, int* error);
+int maavss_peer_destroy(maavss_peer* peer);
+
 typedef struct maavss_comm maavss_comm;
 int maavss_comm_unique_id(void* id128);
 int maavss_comm_init(maavss_comm** comm, int rank, int world, const void* id128);

@@ -297,7 +297,15 @@ class ConvTransposeFn(torch.autograd.Function):
 def _allreduce_partial(partial):
     import torch.distributed as dist
     from . import parallel
-    if parallel.native_comm() is not None and partial.is_cuda:
+    if parallel.peer_exchange() is not None and partial.is_cuda:
+        # one single-CTA kernel over NVLink peer memory per exchange; the two encoder branches run on two streams -> two channels
+        from . import layers
+        cur = torch.cuda.current_stream(partial.device)
+        side = layers._side_streams.get(partial.device)
+        channel = 1 if (side is not None and cur.cuda_stream == side.cuda_stream) else 0
+        if not parallel.peer_allreduce_sum_(partial, channel):
+            parallel.allreduce_sum_(partial)
+    elif parallel.native_comm() is not None and partial.is_cuda:
         parallel.allreduce_sum_(partial)
     else:
         dist.all_reduce(partial, group=SYNC_BN_GROUP)
