@@ -461,7 +461,7 @@ int maavss_flow_pyr_lk(const unsigned char* prev_gray, const unsigned char* next
  *   peer_connect    opens the other ranks' buffers: handles = world x 64 bytes, indexed by rank
  *   peer_allreduce_sum_f64   in place, n <= max_doubles, enqueued on `stream` (capturable).  Exchanges of one channel must be
  *                   issued in the same order on every rank; streams that run concurrently use different channels.
- *   peer_status     *error != 0 after a rank waited ~2 s for a peer and gave up (the results are then garbage, not a hang). */
+ *   peer_status     *error != 0 after a rank waited ~30 s for a peer and gave up (the results are then garbage, not a hang). */
 typedef struct maavss_peer maavss_peer;
 int maavss_peer_create(maavss_peer** peer, int rank, int world, int channels, int max_doubles, void* handle64);
 int maavss_peer_connect(maavss_peer* peer, const void* handles);

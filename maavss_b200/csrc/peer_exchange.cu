@@ -9,7 +9,7 @@
 //   sum    it adds the world's contributions in rank order -- every rank computes the bit-identical sum -- in place
 // The sequence counter lives in device memory and is advanced by the kernel, so a captured CUDA graph replays correctly.
 // Exchanges of one channel must be issued in the same order on every rank; concurrent streams (the two encoder branches)
-// use different channels.  A rank that waits longer than ~2 s sets an error word (maavss_peer_status) and gives up instead
+// use different channels (or one ordered stream).  A rank that waits longer than ~30 s sets an error word (maavss_peer_status) and gives up instead
 // of hanging the GPU.
 #include <stdint.h>
 #include <string.h>
@@ -19,7 +19,10 @@
 namespace px {
 
 constexpr int MAXW = 16, SLOTS = 4, THREADS = 512;
-constexpr long long WAIT_LIMIT = 4000000000LL;       // clock64 ticks (~2 s)
+// clock64 ticks (~30 s).  Long on purpose: like an NCCL collective, an exchange simply waits for a rank that is late (host-side
+// skew between processes can be seconds at start-up); a rank that gave up early would run ahead, lap the 4 slots and leave
+// every later exchange of every rank waiting out its limit.
+constexpr long long WAIT_LIMIT = 60000000000LL;
 
 struct State {
     unsigned long long seq;

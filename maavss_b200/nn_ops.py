@@ -297,14 +297,18 @@ class ConvTransposeFn(torch.autograd.Function):
 def _allreduce_partial(partial):
     import torch.distributed as dist
     from . import parallel
-    if parallel.peer_exchange() is not None and partial.is_cuda:
-        # one single-CTA kernel over NVLink peer memory per exchange; the two encoder branches run on two streams -> two channels
-        from . import layers
+    if parallel.peer_exchange() is not None and partial.is_cuda and partial.numel() <= parallel.peer_capacity():
+        # One single-CTA kernel over NVLink peer memory per exchange.  All exchanges of a rank run on ONE dedicated stream in
+        # host issue order -- the same order on every rank -- whichever branch stream they belong to: two spinning exchange
+        # kernels of different branches that the hardware happened to order differently on two ranks would wait for each
+        # other forever (concurrent execution of graph branches is not guaranteed).
         cur = torch.cuda.current_stream(partial.device)
-        side = layers._side_streams.get(partial.device)
-        channel = 1 if (side is not None and cur.cuda_stream == side.cuda_stream) else 0
-        if not parallel.peer_allreduce_sum_(partial, channel):
-            parallel.allreduce_sum_(partial)
+        ex = parallel.exchange_stream(partial.device)
+        ex.wait_stream(cur)
+        with torch.cuda.stream(ex):
+            parallel.peer_allreduce_sum_(partial, 0)
+        partial.record_stream(ex)
+        cur.wait_stream(ex)
     elif parallel.native_comm() is not None and partial.is_cuda:
         parallel.allreduce_sum_(partial)
     else:

@@ -22,7 +22,7 @@ _WORLD = 1
 _COMM = None        # maavss_comm* (ctypes.c_void_p): the library's own NCCL communicator (csrc/comm.cu)
 _PEER = None        # maavss_peer* : NVLink peer-memory exchange of the BatchNorm partial sums (csrc/peer_exchange.cu)
 _PEER_CAP = 0
-PEER_CHANNELS, PEER_MAX_DOUBLES = 2, 8192
+PEER_CHANNELS, PEER_MAX_DOUBLES = 1, 8192
 
 
 def init(backend=None, sync_bn=True):
@@ -79,6 +79,21 @@ def peer_exchange():
     return _PEER
 
 
+def peer_capacity():
+    return _PEER_CAP
+
+
+_EXCHANGE_STREAMS = {}
+
+
+def exchange_stream(device):
+    """The one stream per device on which every peer-memory exchange runs (total order = host issue order)."""
+    s = _EXCHANGE_STREAMS.get(device)
+    if s is None:
+        s = _EXCHANGE_STREAMS[device] = torch.cuda.Stream(device=device)
+    return s
+
+
 def peer_allreduce_sum_(t, channel):
     """In-place sum of a small fp64 tensor over the ranks through NVLink peer memory; False when it does not qualify."""
     if _PEER is None or not (t.is_cuda and t.is_contiguous() and t.dtype == torch.float64 and 0 < t.numel() <= _PEER_CAP):
@@ -90,7 +105,7 @@ def peer_allreduce_sum_(t, channel):
 
 
 def peer_status():
-    """0 = fine; non-zero = a rank gave up waiting for a peer (see csrc/peer_exchange.cu)."""
+    """0 = fine; non-zero = a rank gave up waiting ~30 s for a peer (see csrc/peer_exchange.cu)."""
     if _PEER is None:
         return 0
     import ctypes
