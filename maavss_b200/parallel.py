@@ -221,13 +221,16 @@ class EarlyGradAllReduce:
     `finish()` is the rest of the optimizer step: exchange of what is left, Adam + zero_grad of what is left, joined with
     the side stream.  Everything is captured when the step is recorded into a CUDA graph."""
 
-    def __init__(self, optimizer, offset, early_adam=True, head_offset=None):
+    def __init__(self, optimizer, offset, early_adam=True, head_offset=None, out_offset=None):
         # the early Adam pays only on one GPU: behind the heads' all-reduce (N > 1) it would land in the encoder backward, whose
         # im2col matrices live in L2 (measured at N = 2: 2.54 ms/step with it, 2.46 without)
         self.opt, self.offset, self.early_adam = optimizer, int(offset), early_adam and EARLY_ADAM and _GROUP is None
         self.head_offset = int(head_offset) if head_offset is not None else None
+        # [out_offset, end): the output heads a_fc1 / v_fc1 (70 % of all parameters), final even earlier -- when the gradient
+        # of their common input exists (start_outputs)
+        self.out_offset = int(out_offset) if (out_offset is not None and head_offset is not None and out_offset > head_offset) else None
         self.side = torch.cuda.Stream()
-        self.started = self.heads_started = False
+        self.started = self.heads_started = self.outputs_started = False
         if _GROUP is not None:
             optimizer.grad_scale = 1.0 / _WORLD
 
@@ -235,17 +238,27 @@ class EarlyGradAllReduce:
         self.side.wait_stream(torch.cuda.current_stream())
         nn_ops.join_wgrad_streams(target=self.side, clear=False)      # this part's weight gradients may still be in flight
 
+    def _tail(self, lo, hi, prepare):
+        self._fork()
+        with torch.cuda.stream(self.side):
+            if _GROUP is not None:
+                allreduce_sum_(self.opt.flat.grad[lo:hi])
+            if self.early_adam:
+                if prepare:
+                    self.opt.prepare()
+                self.opt.apply_range(lo, hi, zero_grad=True, max_ctas=EARLY_ADAM_CTAS)
+
+    def start_outputs(self):
+        if self.outputs_started or self.heads_started or self.out_offset is None or (_GROUP is None and not self.early_adam):
+            return
+        self.outputs_started = True
+        self._tail(self.out_offset, None, True)
+
     def start_heads(self):
         if self.heads_started or self.head_offset is None or (_GROUP is None and not self.early_adam):
             return
         self.heads_started = True
-        self._fork()
-        with torch.cuda.stream(self.side):
-            if _GROUP is not None:
-                allreduce_sum_(self.opt.flat.grad[self.head_offset:])
-            if self.early_adam:
-                self.opt.prepare()
-                self.opt.apply_range(self.head_offset, None, zero_grad=True, max_ctas=EARLY_ADAM_CTAS)
+        self._tail(self.head_offset, self.out_offset if self.outputs_started else None, not self.outputs_started)
 
     def start(self):
         if self.started or _GROUP is None:
@@ -253,22 +266,26 @@ class EarlyGradAllReduce:
         self.started = True
         self._fork()
         with torch.cuda.stream(self.side):
-            allreduce_sum_(self.opt.flat.grad[self.offset:self.head_offset if self.heads_started else None])
+            hi = self.head_offset if self.heads_started else (self.out_offset if self.outputs_started else None)
+            allreduce_sum_(self.opt.flat.grad[self.offset:hi])
 
     def finish(self):
         """Everything of optimizer.step(); optimizer.zero_grad() (and the gradient exchange) that the hooks have not done."""
         opt, g = self.opt, self.opt.flat.grad
         if _GROUP is not None:
-            left = self.offset if self.started else (self.head_offset if self.heads_started else g.numel())
+            left = self.offset if self.started else (self.head_offset if self.heads_started else
+                                                    (self.out_offset if self.outputs_started else g.numel()))
             if left > 0:
                 allreduce_sum_(g[:left])
-        if self.started or self.heads_started:
+        if self.started or self.heads_started or self.outputs_started:
             torch.cuda.current_stream().wait_stream(self.side)
         if self.heads_started and self.early_adam:
             opt.apply_range(0, self.head_offset, zero_grad=True)
+        elif self.outputs_started and self.early_adam:
+            opt.apply_range(0, self.out_offset, zero_grad=True)
         else:
             opt.step_and_zero_grad()
-        self.started = self.heads_started = False
+        self.started = self.heads_started = self.outputs_started = False
 
 
 def allreduce_max_(t):

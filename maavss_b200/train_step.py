@@ -129,7 +129,14 @@ class FusionTrainStep(_TrainStepBase):
         tail_ok = {id(p) for mod in (m.fc1, m.fc2, m.a_fc1, m.v_fc1, m.stft_decoder, m.phasegram_decoder) for p in mod.parameters()}
         if head_off < off or any(id(p) not in tail_ok for p, o in zip(flat.params, flat.offsets) if o >= head_off):
             head_off = None
-        self.early = parallel.EarlyGradAllReduce(self.opt, off, head_offset=head_off)
+        out_off = None
+        if head_off is not None:
+            outs = {id(p) for mod in (m.a_fc1, m.v_fc1) for p in mod.parameters()}
+            first_out = min((o for p, o in zip(flat.params, flat.offsets) if id(p) in outs), default=None)
+            # the output heads must be the END of the arena for their range [first_out, numel) to hold nothing else
+            if first_out is not None and all(id(p) in outs for p, o in zip(flat.params, flat.offsets) if o >= first_out):
+                out_off = first_out
+        self.early = parallel.EarlyGradAllReduce(self.opt, off, head_offset=head_off, out_offset=out_off)
 
         def pre_hook(mod, args):
             x = args[0]
@@ -170,7 +177,10 @@ class FusionTrainStep(_TrainStepBase):
         ya = nn_ops.stack_windows(y_stft, G, self.hpf, span)
         nn_ops.BN_GROUPS = G
         try:
-            yh_a, yh_v, _ = self.model(xa, pgram)
+            yh_a, yh_v, fused = self.model(xa, pgram)
+            if self.early is not None and fused.requires_grad:
+                # both output heads have back-propagated when the gradient of their common input exists
+                fused.register_hook(lambda g: (self.early.start_outputs() if self._running else None, None)[1])
             # What the sequential loop reports -- the last window's losses -- is a side-stream job: the backward pass is
             # seeded with d loss / d yh directly (same kernel and seeds as MSELoss.backward under loss.backward()), so no
             # loss reduction sits between the forward and the backward pass.
