@@ -79,7 +79,7 @@ class _Profiler:
             "maavss_dft_plan_create", "maavss_dft_plan_destroy", "maavss_gemm_tf32x3_supported", "maavss_gemm_tf32x3_workspace_bytes",
             "maavss_conv_tc_supported", "maavss_conv_tc_workspace_bytes", "maavss_conv_wgrad_tc_supported",
             "maavss_conv_wgrad_tc_workspace_bytes", "maavss_conv_tc3_supported", "maavss_conv_tc3_col_elems",
-            "maavss_conv_tc3_workspace_bytes", "maavss_channel_sum_static_max_channels", "maavss_bilstm_recurrent_supported"}
+            "maavss_conv_tc3_workspace_bytes", "maavss_channel_sum_static_max_channels", "maavss_bilstm_recurrent_supported", "maavss_conv_tc3_permute_weights", "maavss_peer_capacity"}
 
     def __init__(self, real):
         self.real, self.records = real, []
