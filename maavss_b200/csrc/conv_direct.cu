@@ -37,14 +37,19 @@ static Geo make_geo(const maavss_conv_desc* d) {
 }
 
 // ---------------------------------------------------------------------------------------------- WGRAD
-constexpr int WG_CO = 4, WG_J = 18, WG_T = 256;
+constexpr int WG_J = 18, WG_T = 256;
 
-__global__ void __launch_bounds__(WG_T) wgrad_kernel(Geo g, const float* __restrict__ x, const float* __restrict__ dy,
+// CO = output channels per thread block of dW: 4, or 2 for the C1->2 layers (half the accumulators: one more CTA per SM).
+// NQ positions per loop trip (2 for CO = 2; 1 for CO = 4, whose 72 accumulators leave no registers), all their loads issued before the FMAs: the loop is one memory latency per trip otherwise
+// (measured ~1 us per trip at 16 warps per SM), and the grid is sized to ONE wave of resident CTAs by the launcher -- 512 CTAs
+// at 2 per SM ran as two waves, which was most of the 33 us of the C1->2 layer.
+template <int CO, int NQ>
+__global__ void __launch_bounds__(WG_T, 2) wgrad_kernel(Geo g, const float* __restrict__ x, const float* __restrict__ dy,
                                                      float* __restrict__ dw, int P, int pos_per_cta, int J) {
     __shared__ int4 jtab[WG_J];                         // {x offset of (ci, tap) or -1, kd, kh, kw}
-    __shared__ float red[WG_T / 32][WG_CO * WG_J];
+    __shared__ float red[WG_T / 32][CO * WG_J];
     const maavss_conv_desc& d = g.d;
-    const int j0 = blockIdx.y * WG_J, co0 = blockIdx.z * WG_CO;
+    const int j0 = blockIdx.y * WG_J, co0 = blockIdx.z * CO;
     if (threadIdx.x < WG_J) {
         const int j = j0 + threadIdx.x;
         int4 e = make_int4(-1, 0, 0, 0);
@@ -57,51 +62,71 @@ __global__ void __launch_bounds__(WG_T) wgrad_kernel(Geo g, const float* __restr
         jtab[threadIdx.x] = e;
     }
     __syncthreads();
-    float acc[WG_CO][WG_J];
+    float acc[CO][WG_J];
 #pragma unroll
-    for (int u = 0; u < WG_CO; ++u)
+    for (int u = 0; u < CO; ++u)
 #pragma unroll
         for (int jj = 0; jj < WG_J; ++jj) acc[u][jj] = 0.f;
     const int p_begin = blockIdx.x * pos_per_cta, p_end = min(P, p_begin + pos_per_cta);
-    for (int p = p_begin + (int)threadIdx.x; p < p_end; p += WG_T) {
-        const int n = p / g.O;
-        const int o = p - n * g.O;
-        const int a = o / g.OHW;
-        const int r = o - a * g.OHW;
-        const int b = r / d.OW, c = r - b * d.OW;
-        const int id0 = a * d.SD - d.PD, ih0 = b * d.SH - d.PH, iw0 = c * d.SW - d.PW;
-        const float* xp = x + ((size_t)n * d.Cin * g.I + id0 * g.HW + ih0 * d.W + iw0);
-        float dyv[WG_CO];
+    for (int p0 = p_begin + (int)threadIdx.x; p0 < p_end; p0 += NQ * WG_T) {
+        float dyv[NQ][CO], xv[NQ][WG_J];
 #pragma unroll
-        for (int u = 0; u < WG_CO; ++u)
-            dyv[u] = (co0 + u < d.Cout) ? __ldg(dy + ((size_t)n * d.Cout + co0 + u) * g.O + o) : 0.f;
+        for (int q = 0; q < NQ; ++q) {
+            const int p = p0 + q * WG_T;
+            const bool live = p < p_end;
+            const int pp = live ? p : p0;
+            const int n = pp / g.O;
+            const int o = pp - n * g.O;
+            const int a = o / g.OHW;
+            const int r = o - a * g.OHW;
+            const int b = r / d.OW, c = r - b * d.OW;
+            const int id0 = a * d.SD - d.PD, ih0 = b * d.SH - d.PH, iw0 = c * d.SW - d.PW;
+            const float* xp = x + ((size_t)n * d.Cin * g.I + id0 * g.HW + ih0 * d.W + iw0);
 #pragma unroll
-        for (int jj = 0; jj < WG_J; ++jj) {
-            const int4 e = jtab[jj];
-            float xv = 0.f;
-            if (e.x >= 0 && (unsigned)(id0 + e.y) < (unsigned)d.D && (unsigned)(ih0 + e.z) < (unsigned)d.H &&
-                (unsigned)(iw0 + e.w) < (unsigned)d.W)
-                xv = __ldg(xp + e.x);
+            for (int u = 0; u < CO; ++u)
+                dyv[q][u] = (live && co0 + u < d.Cout) ? __ldg(dy + ((size_t)n * d.Cout + co0 + u) * g.O + o) : 0.f;
 #pragma unroll
-            for (int u = 0; u < WG_CO; ++u) acc[u][jj] = fmaf(dyv[u], xv, acc[u][jj]);
+            for (int jj = 0; jj < WG_J; ++jj) {
+                const int4 e = jtab[jj];
+                float v = 0.f;
+                if (live && e.x >= 0 && (unsigned)(id0 + e.y) < (unsigned)d.D && (unsigned)(ih0 + e.z) < (unsigned)d.H &&
+                    (unsigned)(iw0 + e.w) < (unsigned)d.W)
+                    v = __ldg(xp + e.x);
+                xv[q][jj] = v;
+            }
         }
+#pragma unroll
+        for (int q = 0; q < NQ; ++q)
+#pragma unroll
+            for (int jj = 0; jj < WG_J; ++jj)
+#pragma unroll
+                for (int u = 0; u < CO; ++u) acc[u][jj] = fmaf(dyv[q][u], xv[q][jj], acc[u][jj]);
     }
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 #pragma unroll
-    for (int u = 0; u < WG_CO; ++u)
+    for (int u = 0; u < CO; ++u)
 #pragma unroll
         for (int jj = 0; jj < WG_J; ++jj) {
             const float s = warp_sum(acc[u][jj]);
             if (lane == 0) red[warp][u * WG_J + jj] = s;
         }
     __syncthreads();
-    if (threadIdx.x < WG_CO * WG_J) {
+    if (threadIdx.x < CO * WG_J) {
         float s = 0.f;
 #pragma unroll
         for (int w = 0; w < WG_T / 32; ++w) s += red[w][threadIdx.x];
         const int u = threadIdx.x / WG_J, jj = threadIdx.x - u * WG_J;
         if (co0 + u < d.Cout && j0 + jj < J) atomicAdd(dw + (size_t)(co0 + u) * J + j0 + jj, s);
     }
+}
+
+template <int CO, int NQ>
+static int resident_ctas_per_sm() {
+    static int n = 0;
+    if (n == 0) {
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, wgrad_kernel<CO, NQ>, WG_T, 0) != cudaSuccess || n < 1) n = 2;
+    }
+    return n;
 }
 
 }  // namespace direct
@@ -111,13 +136,19 @@ int maavss_conv_wgrad_direct(const maavss_conv_desc* d, const float* x, const fl
     direct::Geo g = direct::make_geo(d);
     const long long P = (long long)d->N * g.O;
     const int J = d->Cin * g.KV;
-    const int gy = ceil_div(J, direct::WG_J), gz = ceil_div(d->Cout, direct::WG_CO);
+    const int CO = d->Cout <= 2 ? 2 : 4;
+    const int gy = ceil_div(J, direct::WG_J), gz = ceil_div(d->Cout, CO);
     // envelope (measured on B200, bench.py --breakdown): every (column block, channel block) pair walks all positions
     // and re-reads dy / x, so the kernel wins for the thin layers (<= 24 block pairs: C1->2 ... C8->16 with 1x9 taps,
     // C2->8 with 5x5) by 4-30x and loses 20-30 % to the tiled implicit GEMM beyond that
     if (P >= (1LL << 31) || (long long)gy * gz > 24 || (long long)gy * gz * P > (16LL << 20)) return 0;
     const int sms = maavss_num_sms();
-    long long want_x = (4LL * sms + (long long)gy * gz - 1) / ((long long)gy * gz);      // ~4 CTAs per SM overall
+    const int occ = CO == 2 ? direct::resident_ctas_per_sm<2, 2>() : direct::resident_ctas_per_sm<4, 1>();
+    static const int waves_pct = [] {                    // tuning knob (benchmarks only): MAAVSS_WGRAD_WAVE_PCT, % of one resident wave
+        const char* e = getenv("MAAVSS_WGRAD_WAVE_PCT");
+        return e ? atoi(e) : 100;
+    }();
+    long long want_x = ((long long)occ * sms * waves_pct / 100) / ((long long)gy * gz);   // one wave of resident CTAs overall
     if (want_x < 1) want_x = 1;
     long long ppc = (P + want_x - 1) / want_x;
     if (ppc < 8 * direct::WG_T) ppc = 8 * direct::WG_T;                                   // >= 8 positions per thread
@@ -130,7 +161,8 @@ int maavss_conv_wgrad_direct(const maavss_conv_desc* d, const float* x, const fl
         }
     }
     dim3 grid(ceil_div(P, ppc), gy, gz);
-    direct::wgrad_kernel<<<grid, direct::WG_T, 0, st>>>(g, x, dy, dw, (int)P, (int)ppc, J);
+    if (CO == 2) direct::wgrad_kernel<2, 2><<<grid, direct::WG_T, 0, st>>>(g, x, dy, dw, (int)P, (int)ppc, J);
+    else direct::wgrad_kernel<4, 1><<<grid, direct::WG_T, 0, st>>>(g, x, dy, dw, (int)P, (int)ppc, J);
     MAAVSS_LAUNCH_CHECK();
     return 1;
 }
