@@ -199,8 +199,8 @@ def allreduce_gradients(optimizer):
     optimizer.grad_scale = 1.0 / _WORLD
 
 
-# CTAs of the early Adam pass (0 = the kernel's own grid): 2 per SM measured best beside the LSTM backward (2.21 vs 2.25 ms/step)
-EARLY_ADAM_CTAS = int(os.environ.get("MAAVSS_EARLY_ADAM_CTAS", "296"))
+# CTAs of the early Adam pass (0 = the kernel's own grid): 3 per SM measured best beside the LSTM backward (2.140 ms/step; 2.156 at 2 per SM, 2.25 unbounded)
+EARLY_ADAM_CTAS = int(os.environ.get("MAAVSS_EARLY_ADAM_CTAS", "444"))
 EARLY_ADAM = os.environ.get("MAAVSS_EARLY_ADAM", "1") != "0"
 
 
