@@ -13,6 +13,7 @@
 // the GEMM that follows, and is kept for the weight gradient.  The SIMT kernels (conv_direct.cu / conv_igemm.cu) did these
 // layers at ~10 TFLOP/s; here the GEMMs are tensor-pipe work and the layer is bound by the col / dcol streams.
 #include <stdint.h>
+#include <stdlib.h>
 #include "common.cuh"
 #include "../../include/maavss_b200.h"
 
@@ -85,6 +86,8 @@ __global__ void __launch_bounds__(256) im2col_staged_kernel(Geo g, const float* 
         const int kh = tap / g.KW, kw = tap - kh * g.KW;
         offs[k] = (ci * g.KH + kh) * span + kw;
     }
+    // (flat loop on purpose: a warp-per-row walk without the divisions measured SLOWER -- st4 forward 48 vs 35 us -- short rows
+    // leave lanes idle and serialise the load latency per row)
     for (int e = threadIdx.x; e < rows * span; e += 256) {
         const int r = e / span, j = e - r * span;
         const int ci = r / g.KH, kh = r - ci * g.KH;
@@ -144,31 +147,36 @@ __global__ void __launch_bounds__(256) rows_kernel(const float* __restrict__ in,
 // (dcol from the product with the permuted weights: channel index fastest).  CTA = 32 consecutive input positions q of one
 // sample x CL input channels; lanes run along ci, so every load of a warp is one contiguous 64 / 128-byte piece of a dcol
 // row; the sums meet in a shared-memory tile and leave coalesced along q.  Deterministic (a gather, no atomics).
-template <int CL>
+// SHT / SWT: compile-time strides (1 or 2; 0 = read them from g).  ncu on the first version: 73 % issue-active, ~200
+// instructions per output element, most of them runtime divisions by the strides and by W -- here the strides are shifts and
+// (ih, iw) of the thread's positions advance by constants.
+template <int CL, int SHT, int SWT>
 __global__ void __launch_bounds__(256) col2im_kernel(Geo g, const float* __restrict__ dcol, float* __restrict__ dx) {
     __shared__ float tile[CL][33];
     constexpr int JP = 256 / CL, NJ = 32 / JP;
+    const int SH = SHT ? SHT : g.SH, SW = SWT ? SWT : g.SW;
     const int c = threadIdx.x % CL, j0 = threadIdx.x / CL;
     const int n = blockIdx.z, q0 = blockIdx.x * 32, cb = blockIdx.y * CL;
     const int ci = cb + c;
     const float* base = dcol + (size_t)n * g.OHW * g.Kc + ci;
-    const long long step = (long long)g.Kc - (long long)g.SW * g.Cin;      // ow + 1: next dcol row, kw - SW
+    const int step = g.Kc - SW * g.Cin;                                     // ow + 1: next dcol row, kw - SW
+    const long long rstep = (long long)g.OW * g.Kc - (long long)SH * g.KW * g.Cin;      // oh + 1: next output row, kh - SH
+    int q = q0 + j0;
+    int ih = q / g.W, iw = q - ih * g.W;                                    // one division per thread; then += JP with carry
+    const int dq_h = JP / g.W, dq_w = JP - dq_h * g.W;
     float acc[NJ];
     // the thread's NJ positions side by side: their loads (up to 5 per row of taps) are all in flight together
 #pragma unroll
     for (int u = 0; u < NJ; ++u) {
-        const int q = q0 + j0 + u * JP;
         acc[u] = 0.f;
         if (q < g.I && ci < g.Cin) {
-            const int ih = q / g.W, iw = q - ih * g.W;
             // output rows / columns that reach (ih, iw): oh in [oh_lo, oh_hi], kh = ih + PH - oh*SH, likewise along W
             const int th = ih + g.PH, tw = iw + g.PW;
-            const int oh_hi = min(g.OH - 1, th / g.SH), ow_hi = min(g.OW - 1, tw / g.SW);
-            const int oh_lo = th - g.KH + 1 <= 0 ? 0 : (th - g.KH + g.SH) / g.SH;
-            const int ow_lo = tw - g.KW + 1 <= 0 ? 0 : (tw - g.KW + g.SW) / g.SW;
+            const int oh_hi = min(g.OH - 1, th / SH), ow_hi = min(g.OW - 1, tw / SW);
+            const int oh_lo = th - g.KH + 1 <= 0 ? 0 : (th - g.KH + SH) / SH;
+            const int ow_lo = tw - g.KW + 1 <= 0 ? 0 : (tw - g.KW + SW) / SW;
             const int cnt = ow_hi - ow_lo + 1;
-            const float* p0 = base + (size_t)(oh_lo * g.OW + ow_lo) * g.Kc + (size_t)((th - oh_lo * g.SH) * g.KW + tw - ow_lo * g.SW) * g.Cin;
-            const long long rstep = (long long)g.OW * g.Kc - (long long)g.SH * g.KW * g.Cin;      // oh + 1: next output row, kh - SH
+            const float* p0 = base + (size_t)(oh_lo * g.OW + ow_lo) * g.Kc + ((th - oh_lo * SH) * g.KW + tw - ow_lo * SW) * g.Cin;
             for (int oh = oh_lo; oh <= oh_hi; ++oh, p0 += rstep) {
                 float v[5];
 #pragma unroll
@@ -178,6 +186,13 @@ __global__ void __launch_bounds__(256) col2im_kernel(Geo g, const float* __restr
                 for (int i = 5; i < cnt; ++i) acc[u] += __ldg(p0 + i * step);
             }
         }
+        q += JP;
+        ih += dq_h;
+        iw += dq_w;
+        if (iw >= g.W) {
+            iw -= g.W;
+            ++ih;
+        }
     }
 #pragma unroll
     for (int u = 0; u < NJ; ++u) tile[c][j0 + u * JP] = acc[u];
@@ -186,6 +201,15 @@ __global__ void __launch_bounds__(256) col2im_kernel(Geo g, const float* __restr
         const int cc = e >> 5, jj = e & 31;
         if (cb + cc < g.Cin && q0 + jj < g.I) dx[((size_t)n * g.Cin + cb + cc) * g.I + q0 + jj] = tile[cc][jj];
     }
+}
+
+template <int CL>
+static void launch_col2im(const Geo& g, const float* dcol, float* dx, cudaStream_t st) {
+    dim3 grid((g.I + 31) / 32, (g.Cin + CL - 1) / CL, g.N);
+    if (g.SH == 1 && g.SW == 2) col2im_kernel<CL, 1, 2><<<grid, 256, 0, st>>>(g, dcol, dx);
+    else if (g.SH == 2 && g.SW == 2) col2im_kernel<CL, 2, 2><<<grid, 256, 0, st>>>(g, dcol, dx);
+    else if (g.SH == 1 && g.SW == 1) col2im_kernel<CL, 1, 1><<<grid, 256, 0, st>>>(g, dcol, dx);
+    else col2im_kernel<CL, 0, 0><<<grid, 256, 0, st>>>(g, dcol, dx);
 }
 
 static inline size_t al256(size_t v) { return (v + 255) & ~(size_t)255; }
@@ -243,6 +267,7 @@ extern "C" int maavss_conv_tc3_fwd(const maavss_conv_desc* d, const float* x, co
     while (OWT > 8 && (long long)g.N * g.OH * ((g.OW + OWT - 1) / OWT) < 1500) OWT /= 2;      // >= ~10 CTAs per SM: the staging phase is latency bound
     int span = (OWT - 1) * g.SW + g.KW;
     size_t smem = sizeof(float) * ((size_t)g.Kc + (size_t)g.Cin * g.KH * span);
+    // (ncu: this kernel is instruction-issue bound, 72 % issue-active, ~50 instructions per float4 of col.)
     if (smem <= 48 * 1024 && (long long)g.N * g.OH * ((g.OW + OWT - 1) / OWT) < (1LL << 31)) {
         const unsigned grid = (unsigned)(g.N * g.OH * ((g.OW + OWT - 1) / OWT));
         tc3::im2col_staged_kernel<<<grid, 256, smem, st>>>(g, x, col, OWT, span);
@@ -276,16 +301,9 @@ extern "C" int maavss_conv_tc3_dgrad(const maavss_conv_desc* d, const float* dy_
     int rc = maavss_gemm_tf32x3(dy_rows, 0, g.Cout, w_perm, 1, g.Kc, (int)g.pos, g.Kc, g.Cout, dcol, g.Kc, 0, nullptr, 0, MAAVSS_ACT_NONE, 0.f, 0, gws,
                                 workspace_bytes - 256 - (long long)dcol_bytes, stream);
     if (rc) return rc;
-    if (g.Cin >= 32) {
-        dim3 grid((g.I + 31) / 32, (g.Cin + 31) / 32, g.N);
-        tc3::col2im_kernel<32><<<grid, 256, 0, st>>>(g, dcol, dx);
-    } else if (g.Cin <= 8) {
-        dim3 grid((g.I + 31) / 32, (g.Cin + 7) / 8, g.N);
-        tc3::col2im_kernel<8><<<grid, 256, 0, st>>>(g, dcol, dx);
-    } else {
-        dim3 grid((g.I + 31) / 32, (g.Cin + 15) / 16, g.N);
-        tc3::col2im_kernel<16><<<grid, 256, 0, st>>>(g, dcol, dx);
-    }
+    if (g.Cin >= 32) tc3::launch_col2im<32>(g, dcol, dx, st);
+    else if (g.Cin <= 8) tc3::launch_col2im<8>(g, dcol, dx, st);
+    else tc3::launch_col2im<16>(g, dcol, dx, st);
     MAAVSS_LAUNCH_CHECK();
     return MAAVSS_OK;
 }
