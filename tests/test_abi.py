@@ -61,3 +61,40 @@ def test_no_cpu_fallback(built):
         pytest.skip("GPU present")
     with pytest.raises(Exception):
         audio_ops.stft_planes(torch.zeros(1, 1000), torch.hamming_window(256), 256, 66)
+
+
+def test_envelopes_of_the_tensor_core_paths(built):
+    """Host-side envelope predicates of the C ABI (pure arithmetic, no GPU): which encoder layers of the headline model take
+    the 3xTF32 tensor-core path (conv_tc3.cu), which stay on the direct kernels, and the limits the header states."""
+    from maavss_b200 import _specs
+    from maavss_b200 import nn_ops as ops
+    from maavss_b200._lib import lib
+    L = lib()
+    B = 64                                       # 16 clips x 4 stacked accumulation windows
+    sp = _specs.fusion_specs([B, 2, 64, 128], [B, 1, 8, 4096], 64, 4096, "fc")
+    took = {}
+    for name, specs, hw in (("pg", sp["pg_enc"], (8, 4096)), ("st", sp["st_enc"], (64, 128))):
+        h, w = hw
+        for i, s in enumerate(specs):
+            oh, ow = _specs.conv_out(h, s["k"][0], s["s"][0], s["p"][0]), _specs.conv_out(w, s["k"][1], s["s"][1], s["p"][1])
+            desc = ops.make_conv_desc((B, s["cin"], 1, h, w), (s["cout"], s["cin"], 1, *s["k"]), (1, *s["s"]), (0, *s["p"]), (1, oh, ow))
+            took[f"{name}{i + 1}"] = bool(L.maavss_conv_tc3_supported(ctypes.byref(desc)))
+            if took[f"{name}{i + 1}"]:
+                assert L.maavss_conv_tc3_col_elems(ctypes.byref(desc)) == B * oh * ow * s["cin"] * s["k"][0] * s["k"][1]
+                assert all(L.maavss_conv_tc3_workspace_bytes(ctypes.byref(desc), m) >= 256 for m in range(3))
+            h, w = oh, ow
+    assert [k for k, v in took.items() if v] == ["pg5", "pg6", "pg7", "pg8", "pg9", "pg10", "st2", "st3", "st4", "st5"]
+    # 3-D kernels, thin layers and ragged output maps are outside the envelope
+    d3 = ops.make_conv_desc((2, 16, 8, 32, 32), (32, 16, 3, 5, 5), (1, 1, 1), (1, 2, 2), (8, 32, 32))
+    assert L.maavss_conv_tc3_supported(ctypes.byref(d3)) == 0
+    odd = ops.make_conv_desc((2, 32, 1, 9, 11), (32, 32, 1, 3, 3), (1, 1, 1), (0, 0, 0), (1, 7, 9))
+    assert L.maavss_conv_tc3_supported(ctypes.byref(odd)) == 0
+    # GEMM: pitches in multiples of 4 floats; row-major output needs Q % 4 == 0
+    assert L.maavss_gemm_tf32x3_supported(64, 32768, 512, 0, 512, 0, 512, 32768, 0) == 1
+    assert L.maavss_gemm_tf32x3_supported(64, 130, 512, 0, 512, 0, 512, 130, 0) == 0
+    assert L.maavss_gemm_tf32x3_supported(64, 130, 512, 0, 512, 0, 512, 64, 1) == 1
+    assert L.maavss_gemm_tf32x3_supported(64, 128, 510, 0, 510, 0, 510, 128, 0) == 0
+    assert L.maavss_gemm_tf32x3_workspace_bytes(32768, 64, 512) == 0            # enough tiles: no split-K
+    assert L.maavss_gemm_tf32x3_workspace_bytes(512, 64, 4096) > 0
+    assert L.maavss_bilstm_recurrent_supported(64, 8, 256) == 1 and L.maavss_bilstm_recurrent_supported(64, 8, 128) == 0
+    assert L.maavss_channel_sum_static_max_channels() == 4096
