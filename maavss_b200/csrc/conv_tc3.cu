@@ -88,9 +88,18 @@ __global__ void __launch_bounds__(256) im2col_staged_kernel(Geo g, const float* 
     }
     // (flat loop on purpose: a warp-per-row walk without the divisions measured SLOWER -- st4 forward 48 vs 35 us -- short rows
     // leave lanes idle and serialise the load latency per row)
+    const float inv_span = 1.0f / (float)span, inv_kh = 1.0f / (float)g.KH;
     for (int e = threadIdx.x; e < rows * span; e += 256) {
-        const int r = e / span, j = e - r * span;
-        const int ci = r / g.KH, kh = r - ci * g.KH;
+        // e / span and r / KH through the fp32 reciprocal + one correction step (exact: e < 2^16): the integer divisions were
+        // ~40 of the ~50 issue slots per staged element
+        int r = __float2int_rz((float)e * inv_span);
+        r += (r + 1) * span <= e;
+        r -= r * span > e;
+        const int j = e - r * span;
+        int ci = __float2int_rz((float)r * inv_kh);
+        ci += (ci + 1) * g.KH <= r;
+        ci -= ci * g.KH > r;
+        const int kh = r - ci * g.KH;
         const int ih = ih0 + kh, iw = iw0 + j;
         win[e] = (ih >= 0 && ih < g.H && iw >= 0 && iw < g.W) ? __ldg(x + (((size_t)n * g.Cin + ci) * g.H + ih) * g.W + iw) : 0.f;
     }
