@@ -57,22 +57,30 @@ def _init_peer_exchange(rank, world):
     L = lib()
     peer = ctypes.c_void_p()
     handle = (ctypes.c_ubyte * 64)()
+
+    def all_ok(flag):
+        t = torch.tensor([1 if flag else 0], dtype=torch.int32, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)          # every rank takes the same decision: all ranks or none
+        return int(t.item()) == 1
+
     try:
         check(L.maavss_peer_create(ctypes.byref(peer), rank, world, PEER_CHANNELS, PEER_MAX_DOUBLES, handle))
-        mine = torch.tensor(list(handle), dtype=torch.uint8, device="cuda")
-        every = torch.empty(world * 64, dtype=torch.uint8, device="cuda")
-        dist.all_gather_into_tensor(every, mine)
-        buf = (ctypes.c_ubyte * (64 * world))(*every.cpu().tolist())
-        ok = torch.ones(1, dtype=torch.int32, device="cuda")
-        try:
-            check(L.maavss_peer_connect(peer, buf))
-        except RuntimeError:
-            ok.zero_()
-        dist.all_reduce(ok, op=dist.ReduceOp.MIN)          # all ranks or none
-        if int(ok.item()) == 1:
-            _PEER, _PEER_CAP = peer, int(L.maavss_peer_capacity(peer))
+        created = True
     except RuntimeError:
-        _PEER = None
+        created = False
+    if not all_ok(created):
+        return
+    mine = torch.tensor(list(handle), dtype=torch.uint8, device="cuda")
+    every = torch.empty(world * 64, dtype=torch.uint8, device="cuda")
+    dist.all_gather_into_tensor(every, mine)
+    buf = (ctypes.c_ubyte * (64 * world))(*every.cpu().tolist())
+    try:
+        check(L.maavss_peer_connect(peer, buf))
+        connected = True
+    except RuntimeError:
+        connected = False
+    if all_ok(connected):
+        _PEER, _PEER_CAP = peer, int(L.maavss_peer_capacity(peer))
 
 
 def peer_exchange():
